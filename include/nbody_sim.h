@@ -1,0 +1,137 @@
+/*
+ * nbody_sim.h -- C-ABI of the CUDA simulation pipeline (libnbody_sim / libnbody.so).
+ *
+ * Section 1 is, name for name and argument for argument, the seam the reference's
+ * world.c binds to reach its GPU simulator (ref src/lib/sim_gpu.h:8-36).  The
+ * reference implements it with Vulkan (src/lib/sim_gpu.c + vulkan_ctx.c + the GLSL
+ * shader); here it is a CUDA context with device-resident SoA buffers and the sm_100a
+ * force+integrator kernel.  Because the signatures are Vulkan-free plain C, the
+ * reference's own world.c links against this library unchanged.
+ *
+ * Section 2 are additions the reference has no counterpart for (device choice, target
+ * sharding across GPUs, asynchronous stepping, pinned host memory, introspection).
+ * Plain pointers and sizes only; no CUDA, torch or NCCL types appear in a signature.
+ *
+ * Error convention (ref src/lib/util.h:17-29): no return codes; any CUDA/NCCL failure
+ * prints "file:line [func] ..." to stderr and abort()s.  There is no CPU fallback:
+ * creating a pipeline on a machine without a usable B200-class device aborts.
+ */
+#ifndef NB_SIM_H
+#define NB_SIM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "nbody.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------- Section 1: the reference seam (sim_gpu.h) ------------------------ */
+
+/* Kernel parameters; only dt may change after creation.  (ref sim_gpu.h:8-12) */
+typedef struct WorldData {
+    uint32_t total_len; /* all particles = targets                         */
+    uint32_t mass_len;  /* leading particles with mass > 0 = sources        */
+    float dt;           /* ignored at creation; passed per PerformSimUpdate */
+} WorldData;
+
+typedef struct SimPipeline SimPipeline; /* ref sim_gpu.h:15 */
+
+/* Allocate device state for DATA.total_len particles (ref sim_gpu.h:21).  The number of
+ * GPUs driven by this process comes from env NBODY_NGPUS (default 1), the first device
+ * from NBODY_DEVICE (default 0): the public API has no parameter for either. */
+SimPipeline *CreateSimPipeline(WorldData data);
+
+/* Free everything; NULL is ignored.  (ref sim_gpu.h:24) */
+void DestroySimPipeline(SimPipeline *sim);
+
+/* Device -> PS: total_len Particles in World order.  (ref sim_gpu.h:27) */
+void GetSimulationData(const SimPipeline *sim, Particle *ps);
+
+/* PS -> device: total_len Particles in World order (massive first).  (ref sim_gpu.h:30) */
+void SetSimulationData(SimPipeline *sim, const Particle *ps);
+
+/* N > 0 chained steps of size DT; returns after the device finished.  Data MUST have
+ * been set before.  (ref sim_gpu.h:32-36, sim_gpu.c:258-361) */
+void PerformSimUpdate(SimPipeline *sim, uint32_t n, float dt);
+
+/* ---------------- Section 2: additions --------------------------------------------- */
+
+#define NB_SIM_UNIQUE_ID_BYTES 128
+
+/* Optional creation parameters; zero-initialise, set struct_size, fill what you need. */
+typedef struct NbSimConfig {
+    uint32_t struct_size;  /* sizeof(NbSimConfig), for forward compatibility            */
+    int32_t device;        /* first CUDA device ordinal; < 0: env NBODY_DEVICE or 0      */
+    int32_t local_gpus;    /* GPUs driven by THIS process; <= 0: env NBODY_NGPUS or 1    */
+    int32_t rank;          /* this process' index among `world` processes (default 0)   */
+    int32_t world;         /* processes sharing the particle set (default 1)             */
+    const void *unique_id; /* NB_SIM_UNIQUE_ID_BYTES from NbSimGetUniqueId on rank 0;    */
+                           /* required iff world > 1                                     */
+    void *stream;          /* cudaStream_t to run on (single-GPU only); NULL: own stream */
+    uint32_t slab_len;     /* sources per partial-sum slab; 0: automatic                 */
+    uint32_t flags;        /* NB_SIM_FLAG_*                                              */
+} NbSimConfig;
+
+#define NB_SIM_FLAG_NO_PEER_STORE 1u /* single process, several GPUs: exchange positions with   */
+                                     /* NCCL instead of peer stores from the kernel epilogue   */
+#define NB_SIM_FLAG_NO_OVERLAP    2u /* do not overlap the position exchange with the massless  */
+                                     /* targets' kernel                                         */
+
+SimPipeline *NbSimCreate(WorldData data, const NbSimConfig *cfg);
+
+/* Fill OUT (NB_SIM_UNIQUE_ID_BYTES) with a fresh NCCL unique id; rank 0 calls this and
+ * ships the bytes to the other ranks by its own means (torch.distributed, MPI, a file). */
+void NbSimGetUniqueId(void *out);
+
+/* Enqueue N steps and return immediately / wait for everything enqueued so far. */
+void NbSimStepAsync(SimPipeline *sim, uint32_t n, float dt);
+void NbSimSynchronize(SimPipeline *sim);
+
+/* Device-side time of the most recent NbSimStepAsync/PerformSimUpdate call in ms (CUDA
+ * events on the launching stream, max over this process' GPUs); synchronises. */
+float NbSimLastStepMs(SimPipeline *sim);
+
+/* Page-locked host memory for Particle arrays, so uploads/downloads run at link speed. */
+void *NbSimHostAlloc(size_t bytes);
+void NbSimHostFree(void *p);
+
+typedef struct NbSimInfo {
+    char device_name[64];
+    int32_t device;         /* first device ordinal                       */
+    int32_t local_gpus;     /* GPUs driven by this process                */
+    int32_t rank, world;    /* process grid                               */
+    int32_t sm_count;       /* multiprocessors on the first device        */
+    int32_t sm_clock_khz;   /* max SM clock reported by the driver        */
+    int32_t cc_major, cc_minor;
+    uint32_t total_len, mass_len;
+    uint32_t tile_targets;  /* targets per CTA (threads x targets/thread) */
+    uint32_t threads;       /* threads per CTA                            */
+    uint32_t slab_len;      /* sources per slab                           */
+    uint32_t slabs;         /* slabs per target tile                      */
+    uint32_t tiles_local;   /* target tiles computed by this process      */
+    uint64_t kernels_launched; /* kernels this pipeline has launched so far */
+    uint64_t pairs_per_step;   /* total_len * mass_len                      */
+} NbSimInfo;
+
+void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);
+
+/* Number of CUDA devices visible to the process (0 when there is no driver/GPU). */
+int32_t NbSimDeviceCount(void);
+
+/* FP64 diagnostics computed on the device from the current state (drift harness):
+ * out[0..1] = sum m v, out[2] = kinetic, out[3] = potential (massive pairs, target
+ * softening), out[4] = sum m, out[5..6] = sum m x.  Synchronises. */
+void NbSimDiagnostics(SimPipeline *sim, double *out7);
+
+/* FP64 accelerations of targets [first, last) from the current device state, written
+ * as (ax, ay) doubles to OUT (2 * (last - first) values).  Does not advance the state. */
+void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* NB_SIM_H */

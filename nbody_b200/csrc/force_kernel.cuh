@@ -1,0 +1,172 @@
+/*
+ * force_kernel.cuh -- the hot path: all-pairs 2D softened gravity + semi-implicit Euler,
+ * hand-written for sm_100a (B200).
+ *
+ * Replaces, in one kernel: the reference compute shader (ref src/shader/particle_cs.glsl:28-55),
+ * its CPU twin PackedUpdate (ref src/lib/sim_cpu.c:156-194) and the per-step buffer copy of
+ * PerformSimUpdate (ref src/lib/sim_gpu.c:314-333).
+ *
+ * Work decomposition.  Targets are cut into tiles of THREADS*T particles; sources [0, mass_len)
+ * are cut into `nslab` slabs.  One CTA = one (target tile, slab) item: it streams the slab through
+ * shared memory in tiles of TJP packs (1 pack = 4 sources: x[4], y[4], G*m[4]) with
+ * cp.async.bulk (TMA 1-D bulk copy) into an NS-deep mbarrier ring, and every thread keeps T
+ * targets in registers.  The pair arithmetic is issued as packed f32x2 instructions
+ * (FADD2/FFMA2/FMUL2: two sources per instruction against one target) so that the FP32 pipe can be
+ * saturated with about half of the issue slots, leaving the rest for MUFU.RSQ and LDS.128:
+ *
+ *     d   = s - t                      2 FADD2         (targets stored negated)
+ *     r2  = dx*dx + (dy*dy + rho_t)    2 FFMA2         (softening = target radius, ref sim_cpu.c:176)
+ *     inv = rsqrt(r2)                  2 MUFU.RSQ
+ *     f   = (inv*inv) * (Gm*inv)       3 FMUL2
+ *     a  += d*f                        2 FFMA2
+ *
+ * = 9 FP32-pipe instructions + 2 MUFU per TWO pairs, 14 algorithmic FLOP per pair.
+ *
+ * Summation order (what makes results independent of the number of GPUs): within a slab a thread
+ * adds even-numbered and odd-numbered sources of its target into the two halves of an f32x2
+ * accumulator, in source order; the slab partial is even+odd; slab partials are added in slab
+ * order.  With nslab > 1 partials go through a scratch buffer and the LAST CTA to finish a target
+ * tile (atomic ticket) adds them and integrates -- the integrator stays fused in this kernel.
+ *
+ * Integrator (ref sim_cpu.c:191-193, particle_cs.glsl:51-54): acc stored; vel += acc*dt;
+ * pos += vel*dt with the new vel; each product and sum individually rounded like the reference's
+ * non-FMA CPU build.  New positions of massive particles are also written to the NEXT source
+ * buffer of every destination in dst_xy[] (this GPU, and peer GPUs over NVLink when they are
+ * mapped), which is both the reference's storage[1]->storage[0] copy and the all-gather.
+ */
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nb {
+
+constexpr int kPack = 4;            /* sources per pack                                  */
+constexpr int kMaxDst = 8;          /* destinations for new source positions (GPUs)      */
+constexpr float kPadPos = 1.0e15f;  /* position of padding sources (G*m = 0): r2 finite,  */
+                                    /* inv^3 finite, contribution exactly +-0              */
+
+struct StepParams {
+    const float4 *src_xy;     /* [src_packs_pad][2]  xs, ys of 4 sources (current step)  */
+    const float4 *src_gm;     /* [src_packs_pad]     G*mass of 4 sources                  */
+    float *dst_xy[kMaxDst];   /* next-step source buffers (as floats), self first         */
+    int ndst;
+    float2 *pos;              /* [total_len] target positions, updated in place           */
+    float2 *vel;              /* [total_len]                                              */
+    float2 *acc;              /* [total_len]                                              */
+    const float *radius;      /* [total_len]                                              */
+    float2 *part;             /* [nslab][n_pad] slab partial sums (nslab > 1)             */
+    unsigned *tile_cnt;       /* [tiles] arrival tickets, zero between steps              */
+    uint32_t total_len, mass_len;
+    uint32_t n_pad;           /* total_len rounded up to the target tile                  */
+    uint32_t src_packs_pad;   /* source packs incl. padding, multiple of TJP              */
+    uint32_t slab_packs;      /* packs per slab (multiple of the inner unroll)            */
+    uint32_t nslab;
+    uint32_t tile_first;      /* first target tile of this launch                         */
+    float dt;
+};
+
+/* ---- PTX helpers: mbarrier, bulk copy, packed math ---------------------------------- */
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "NB_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra NB_DONE_%=;\n"
+        "bra NB_WAIT_%=;\n"
+        "NB_DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+/* TMA 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier. */
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ float rsqrt_mufu(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+/* 4 sources (one pack) against T register-resident targets. */
+template <int T>
+__device__ __forceinline__ void interact_pack(const float4 xs, const float4 ys, const float4 gs,
+                                              const float2 (&ntx)[T], const float2 (&nty)[T],
+                                              const float2 (&rho)[T], float2 (&ax)[T], float2 (&ay)[T]) {
+    const float2 x01 = make_float2(xs.x, xs.y), x23 = make_float2(xs.z, xs.w);
+    const float2 y01 = make_float2(ys.x, ys.y), y23 = make_float2(ys.z, ys.w);
+    const float2 g01 = make_float2(gs.x, gs.y), g23 = make_float2(gs.z, gs.w);
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+        {
+            const float2 dx = __fadd2_rn(x01, ntx[t]);
+            const float2 dy = __fadd2_rn(y01, nty[t]);
+            float2 r2 = __ffma2_rn(dy, dy, rho[t]);
+            r2 = __ffma2_rn(dx, dx, r2);
+            float2 inv;
+            inv.x = rsqrt_mufu(r2.x);
+            inv.y = rsqrt_mufu(r2.y);
+            const float2 inv2 = __fmul2_rn(inv, inv);
+            const float2 gi = __fmul2_rn(g01, inv);
+            const float2 f = __fmul2_rn(inv2, gi);
+            ax[t] = __ffma2_rn(dx, f, ax[t]);
+            ay[t] = __ffma2_rn(dy, f, ay[t]);
+        }
+        {
+            const float2 dx = __fadd2_rn(x23, ntx[t]);
+            const float2 dy = __fadd2_rn(y23, nty[t]);
+            float2 r2 = __ffma2_rn(dy, dy, rho[t]);
+            r2 = __ffma2_rn(dx, dx, r2);
+            float2 inv;
+            inv.x = rsqrt_mufu(r2.x);
+            inv.y = rsqrt_mufu(r2.y);
+            const float2 inv2 = __fmul2_rn(inv, inv);
+            const float2 gi = __fmul2_rn(g23, inv);
+            const float2 f = __fmul2_rn(inv2, gi);
+            ax[t] = __ffma2_rn(dx, f, ax[t]);
+            ay[t] = __ffma2_rn(dy, f, ay[t]);
+        }
+    }
+}
+
+/* Integrate one target and publish it (ref sim_cpu.c:191-193). */
+__device__ __forceinline__ void integrate_store(const StepParams &p, uint32_t i, float2 a) {
+    float2 v = p.vel[i];
+    float2 x = p.pos[i];
+    v.x = __fadd_rn(v.x, __fmul_rn(a.x, p.dt));
+    v.y = __fadd_rn(v.y, __fmul_rn(a.y, p.dt));
+    x.x = __fadd_rn(x.x, __fmul_rn(v.x, p.dt));
+    x.y = __fadd_rn(x.y, __fmul_rn(v.y, p.dt));
+    p.acc[i] = a;
+    p.vel[i] = v;
+    p.pos[i] = x;
+    if (i < p.mass_len) {
+        const uint32_t o = (i >> 2) * 8u + (i & 3u);
+#pragma unroll 1
+        for (int d = 0; d < p.ndst; d++) {
+            p.dst_xy[d][o] = x.x;
+            p.dst_xy[d][o + 4] = x.y;
+        }
+    }
+}
+
+}  // namespace nb

@@ -1,0 +1,711 @@
+/*
+ * sim_cuda.cu -- the CUDA simulation pipeline behind include/nbody_sim.h.
+ *
+ * Replaces the reference's Vulkan simulator (ref src/lib/sim_gpu.c:1-361) and its Vulkan
+ * context/allocator (ref src/lib/vulkan_ctx.c) with: cudaSetDevice + cudaMalloc'd SoA buffers,
+ * one stream per GPU, n-step chaining as n launches on that stream with ping-pong source
+ * buffers (no host round trip, no per-step device copy), lazy AoS download.
+ *
+ * Multi-GPU: targets are sharded by tiles over all GPUs of all cooperating processes; after each
+ * step the new positions of the massive particles are re-replicated -- by peer stores from the
+ * kernel epilogue when the GPUs belong to one process, by an NCCL all-gather (a group of
+ * ncclBroadcast with ragged counts) otherwise -- overlapped with the massless targets' kernel.
+ */
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "layout_kernels.cuh"
+#include "nbody_sim.h"
+#include "nccl_dyn.h"
+#include "step_kernel.cuh"
+#include "util.cuh"
+
+namespace nb {
+
+/* ---- kernel variants ------------------------------------------------------------------ */
+
+struct Variant {
+    const char *name;
+    int threads, T, tjp, ns, unr;
+    size_t smem;
+    const void *func;
+    void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p);
+};
+
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p) {
+    step_kernel<THREADS, T, TJP, NS, MINB, UNR><<<grid, THREADS, step_smem_bytes<TJP, NS>(), st>>>(p);
+}
+
+#define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR)                                              \
+    {                                                                                                 \
+        NAME, THREADS, T, TJP, NS, UNR, step_smem_bytes<TJP, NS>(),                                   \
+            (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR>,                                \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR>                                            \
+    }
+
+static const Variant kVariants[] = {
+    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2), /* default for large N: 1024 targets per CTA */
+    NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2), /* 512 targets per CTA                        */
+    NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2),  /* 256 targets per CTA, small N               */
+    NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2),
+    NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1),
+    NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2),    /* 256 targets per CTA, 2 warps               */
+};
+static const int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
+
+/* ---- geometry ---------------------------------------------------------------------------- */
+
+struct Plan {
+    const Variant *var;
+    uint32_t tile;           /* targets per tile                                    */
+    uint32_t ntiles;         /* all target tiles                                    */
+    uint32_t mtiles;         /* tiles that contain at least one massive particle    */
+    uint32_t n_pad;          /* ntiles * tile                                       */
+    uint32_t src_packs;      /* ceil(mass_len / 4)                                  */
+    uint32_t src_packs_pad;  /* rounded up to the smem tile                         */
+    uint32_t slab_packs, nslab;
+    int ctas_per_sm;
+};
+
+static uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+
+/*
+ * Slab choice.  One launch has tiles*nslab CTAs on slots = SMs * CTAs/SM; the modelled time is
+ * waves * (pairs per CTA + fixed cost).  We minimise the sum over g in {1,2,4,8} GPUs (each g
+ * weighting equally, tiles split g ways) because the slab length fixes the summation order and
+ * must not depend on how many GPUs run the World (results are bit-identical across g).
+ */
+static void choose_slabs(Plan &pl, uint32_t slots, uint32_t forced_slab_len) {
+    const uint32_t unr = 4; /* slab granularity in packs: a multiple of every variant's unroll */
+    if (pl.src_packs == 0) {
+        pl.slab_packs = unr;
+        pl.nslab = 1;
+        return;
+    }
+    if (forced_slab_len) {
+        pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
+        pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
+        return;
+    }
+    const uint32_t min_packs = 32; /* >= 128 sources per slab */
+    const uint32_t max_nslab = std::max(1u, std::min(4096u, pl.src_packs / min_packs));
+    double best = 1e300;
+    uint32_t best_n = 1;
+    for (uint32_t n = 1; n <= max_nslab; n++) {
+        const uint32_t sp = ceil_div(ceil_div(pl.src_packs, n), unr) * unr;
+        const uint32_t ns = ceil_div(pl.src_packs, sp);
+        if (ns != n) continue;
+        const double cta_cost = (double)sp * 4.0 + 64.0 + 2.0 * ns; /* in sources per target */
+        double cost = 0.0;
+        int terms = 0;
+        for (uint32_t g = 1; g <= 8; g *= 2) {
+            const uint32_t tiles = ceil_div(pl.ntiles, g);
+            if (g > 1 && pl.ntiles < 2 * g) break;
+            const double waves = std::ceil((double)tiles * ns / slots);
+            /* ideal = tiles * src_packs*4 / slots */
+            cost += waves * cta_cost * slots / ((double)tiles * pl.src_packs * 4.0);
+            terms++;
+        }
+        cost /= terms;
+        if (cost < best * 0.999) {
+            best = cost;
+            best_n = n;
+        }
+    }
+    pl.slab_packs = ceil_div(ceil_div(pl.src_packs, best_n), unr) * unr;
+    pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
+}
+
+static const Variant *pick_variant(uint32_t total_len, int sm_count) {
+    if (const char *e = getenv("NBODY_VARIANT")) {
+        for (int i = 0; i < kNumVariants; i++)
+            if (strcmp(e, kVariants[i].name) == 0) return &kVariants[i];
+        NB_FAIL("NBODY_VARIANT=%s is not a known kernel variant", e);
+    }
+    /* enough 1024-target tiles to give every SM a few: use the big tile, else the small one */
+    if (total_len >= (uint32_t)sm_count * 1024u * 2u) return &kVariants[0];
+    if (total_len >= (uint32_t)sm_count * 256u) return &kVariants[1];
+    return &kVariants[2];
+}
+
+
+/* ---- pipeline state ------------------------------------------------------------------ */
+
+enum ExchangeMode { kExchangeNone = 0, kExchangePeerStore = 1, kExchangeNccl = 2 };
+
+struct Shard { /* one GPU driven by this process */
+    int device = 0;
+    int global_index = 0; /* rank * local_gpus + local index */
+    cudaStream_t stream = nullptr, comm_stream = nullptr;
+    bool own_stream = true;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_massive = nullptr, ev_comm = nullptr, ev_step = nullptr;
+    Particle *aos = nullptr;
+    float4 *src_xy[2] = {nullptr, nullptr};
+    float4 *src_gm = nullptr;
+    float2 *pos = nullptr, *vel = nullptr, *acc = nullptr, *part = nullptr;
+    float *radius = nullptr;
+    unsigned *tile_cnt = nullptr;
+    double *scratch64 = nullptr;
+    uint32_t a0 = 0, a1 = 0; /* massive target tiles [a0, a1)  */
+    uint32_t b0 = 0, b1 = 0; /* massless target tiles [b0, b1) */
+    NcclComm comm = nullptr;
+};
+
+}  // namespace nb
+
+struct SimPipeline {
+    WorldData data;
+    nb::Plan plan;
+    std::vector<nb::Shard> shards;
+    int rank = 0, world = 1, local_gpus = 1, total_shards = 1;
+    int exchange = nb::kExchangeNone;
+    bool overlap = true;
+    int cur = 0;              /* which src_xy buffer holds the current positions */
+    bool has_data = false;
+    bool timed = false;       /* ev_begin/ev_end recorded at least once          */
+    uint64_t kernels_launched = 0;
+    cudaDeviceProp prop;
+    /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
+    std::vector<uint32_t> all_a0, all_a1, all_b0, all_b1;
+};
+
+namespace nb {
+
+static int env_int(const char *name, int dflt) {
+    const char *e = getenv(name);
+    if (!e || !*e) return dflt;
+    return atoi(e);
+}
+
+static void split_range(uint32_t first, uint32_t count, int parts, int idx, uint32_t *lo, uint32_t *hi) {
+    *lo = first + (uint32_t)(((uint64_t)count * idx) / parts);
+    *hi = first + (uint32_t)(((uint64_t)count * (idx + 1)) / parts);
+}
+
+template <typename Tp>
+static Tp *dev_alloc(size_t count) {
+    Tp *p = nullptr;
+    NB_CUDA(cudaMalloc((void **)&p, std::max<size_t>(count, 1) * sizeof(Tp)));
+    return p;
+}
+
+static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
+    Plan &pl = sim->plan;
+    const uint32_t N = sim->data.total_len, M = sim->data.mass_len;
+    pl.var = pick_variant(N, sim->prop.multiProcessorCount);
+    NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+    int occ = 0;
+    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl.var->func, pl.var->threads, pl.var->smem));
+    NB_ASSERT(occ > 0, "kernel variant %s does not fit on this device", pl.var->name);
+    pl.ctas_per_sm = occ;
+    pl.tile = (uint32_t)pl.var->threads * pl.var->T;
+    pl.ntiles = ceil_div(N, pl.tile);
+    pl.mtiles = ceil_div(M, pl.tile);
+    pl.n_pad = pl.ntiles * pl.tile;
+    pl.src_packs = ceil_div(M, 4);
+    pl.src_packs_pad = std::max(1u, ceil_div(pl.src_packs, (uint32_t)pl.var->tjp)) * pl.var->tjp;
+    choose_slabs(pl, (uint32_t)occ * sim->prop.multiProcessorCount, forced_slab);
+}
+
+}  // namespace nb
+
+/* ---- creation / destruction ---------------------------------------------------------- */
+
+namespace nb {
+
+static void particle_range_of_tiles(const SimPipeline *sim, uint32_t t0, uint32_t t1, uint32_t limit, uint32_t *lo,
+                                    uint32_t *hi) {
+    const uint64_t tile = sim->plan.tile;
+    *lo = (uint32_t)std::min<uint64_t>(t0 * tile, limit);
+    *hi = (uint32_t)std::min<uint64_t>(t1 * tile, limit);
+}
+
+static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
+    NbSimConfig cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.device = -1;
+    if (cfg_in) {
+        NB_ASSERT(cfg_in->struct_size >= 8 && cfg_in->struct_size <= 4096, "NbSimConfig.struct_size not set");
+        memcpy(&cfg, cfg_in, std::min<size_t>(cfg_in->struct_size, sizeof cfg));
+    }
+
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        NB_FAIL("no usable CUDA device (%s); this library has no CPU fallback for the GPU path",
+                e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    NB_ASSERT(data.mass_len <= data.total_len, "mass_len %u > total_len %u", data.mass_len, data.total_len);
+    NB_ASSERT(data.total_len > 0, "a World needs at least one particle");
+
+    SimPipeline *sim = new SimPipeline();
+    sim->data = data;
+    sim->data.dt = 0.f;
+    const int first_dev = cfg.device >= 0 ? cfg.device : env_int("NBODY_DEVICE", 0);
+    sim->local_gpus = cfg.local_gpus > 0 ? cfg.local_gpus : std::max(1, env_int("NBODY_NGPUS", 1));
+    sim->world = std::max(1, cfg.world);
+    sim->rank = cfg.world > 1 ? cfg.rank : 0;
+    NB_ASSERT(sim->rank >= 0 && sim->rank < sim->world, "rank %d outside world %d", sim->rank, sim->world);
+    NB_ASSERT(first_dev >= 0 && first_dev + sim->local_gpus <= ndev, "devices %d..%d requested, %d visible", first_dev,
+              first_dev + sim->local_gpus - 1, ndev);
+    NB_ASSERT(sim->local_gpus <= kMaxDst, "at most %d GPUs per process", kMaxDst);
+    sim->total_shards = sim->world * sim->local_gpus;
+    sim->overlap = !(cfg.flags & NB_SIM_FLAG_NO_OVERLAP) && !env_int("NBODY_NO_OVERLAP", 0);
+
+    NB_CUDA(cudaSetDevice(first_dev));
+    NB_CUDA(cudaGetDeviceProperties(&sim->prop, first_dev));
+    NB_ASSERT(sim->prop.major >= 10, "device %d (%s) is sm_%d%d; this library is built for sm_100a only", first_dev,
+              sim->prop.name, sim->prop.major, sim->prop.minor);
+    make_plan(sim, cfg.slab_len ? cfg.slab_len : (uint32_t)env_int("NBODY_SLAB", 0));
+    const Plan &pl = sim->plan;
+
+    /* who computes which tiles */
+    const int S = sim->total_shards;
+    sim->all_a0.resize(S); sim->all_a1.resize(S); sim->all_b0.resize(S); sim->all_b1.resize(S);
+    for (int q = 0; q < S; q++) {
+        split_range(0, pl.mtiles, S, q, &sim->all_a0[q], &sim->all_a1[q]);
+        split_range(pl.mtiles, pl.ntiles - pl.mtiles, S, q, &sim->all_b0[q], &sim->all_b1[q]);
+    }
+
+    /* exchange mode */
+    if (S == 1) {
+        sim->exchange = kExchangeNone;
+    } else if (sim->world == 1 && !(cfg.flags & NB_SIM_FLAG_NO_PEER_STORE) && !env_int("NBODY_NO_PEER_STORE", 0)) {
+        sim->exchange = kExchangePeerStore;
+        for (int a = 0; a < sim->local_gpus && sim->exchange == kExchangePeerStore; a++)
+            for (int b = 0; b < sim->local_gpus; b++) {
+                int ok = 1;
+                if (a != b) NB_CUDA(cudaDeviceCanAccessPeer(&ok, first_dev + a, first_dev + b));
+                if (!ok) { sim->exchange = kExchangeNccl; break; }
+            }
+    } else {
+        sim->exchange = kExchangeNccl;
+    }
+
+    sim->shards.resize(sim->local_gpus);
+    for (int l = 0; l < sim->local_gpus; l++) {
+        Shard &sh = sim->shards[l];
+        sh.device = first_dev + l;
+        sh.global_index = sim->rank * sim->local_gpus + l;
+        sh.a0 = sim->all_a0[sh.global_index]; sh.a1 = sim->all_a1[sh.global_index];
+        sh.b0 = sim->all_b0[sh.global_index]; sh.b1 = sim->all_b1[sh.global_index];
+        NB_CUDA(cudaSetDevice(sh.device));
+        if (l > 0) {
+            NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+        }
+        if (cfg.stream && sim->local_gpus == 1) {
+            sh.stream = (cudaStream_t)cfg.stream;
+            sh.own_stream = false;
+        } else {
+            NB_CUDA(cudaStreamCreateWithFlags(&sh.stream, cudaStreamNonBlocking));
+        }
+        NB_CUDA(cudaStreamCreateWithFlags(&sh.comm_stream, cudaStreamNonBlocking));
+        NB_CUDA(cudaEventCreate(&sh.ev_begin));
+        NB_CUDA(cudaEventCreate(&sh.ev_end));
+        NB_CUDA(cudaEventCreateWithFlags(&sh.ev_massive, cudaEventDisableTiming));
+        NB_CUDA(cudaEventCreateWithFlags(&sh.ev_comm, cudaEventDisableTiming));
+        NB_CUDA(cudaEventCreateWithFlags(&sh.ev_step, cudaEventDisableTiming));
+        const size_t N = data.total_len;
+        sh.aos = dev_alloc<Particle>(N);
+        sh.src_xy[0] = dev_alloc<float4>((size_t)pl.src_packs_pad * 2);
+        sh.src_xy[1] = dev_alloc<float4>((size_t)pl.src_packs_pad * 2);
+        sh.src_gm = dev_alloc<float4>(pl.src_packs_pad);
+        sh.pos = dev_alloc<float2>(N);
+        sh.vel = dev_alloc<float2>(N);
+        sh.acc = dev_alloc<float2>(N);
+        sh.radius = dev_alloc<float>(N);
+        sh.part = dev_alloc<float2>(pl.nslab > 1 ? (size_t)pl.nslab * pl.n_pad : 1);
+        sh.tile_cnt = dev_alloc<unsigned>(pl.ntiles);
+        sh.scratch64 = dev_alloc<double>(8);
+        NB_CUDA(cudaMemset(sh.tile_cnt, 0, sizeof(unsigned) * pl.ntiles));
+    }
+    if (sim->exchange == kExchangePeerStore) {
+        for (int a = 0; a < sim->local_gpus; a++) {
+            NB_CUDA(cudaSetDevice(first_dev + a));
+            for (int b = 0; b < sim->local_gpus; b++) {
+                if (a == b) continue;
+                cudaError_t pe = cudaDeviceEnablePeerAccess(first_dev + b, 0);
+                if (pe == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+                else NB_CUDA(pe);
+            }
+        }
+    }
+    if (sim->exchange == kExchangeNccl) {
+        NcclApi &api = nccl();
+        if (sim->world == 1) {
+            std::vector<int> devs(sim->local_gpus);
+            std::vector<NcclComm> comms(sim->local_gpus);
+            for (int l = 0; l < sim->local_gpus; l++) devs[l] = first_dev + l;
+            NB_NCCL(api.CommInitAll(comms.data(), sim->local_gpus, devs.data()));
+            for (int l = 0; l < sim->local_gpus; l++) sim->shards[l].comm = comms[l];
+        } else {
+            NB_ASSERT(cfg.unique_id != nullptr, "world > 1 needs NbSimConfig.unique_id from NbSimGetUniqueId");
+            NcclUniqueId id;
+            memcpy(&id, cfg.unique_id, sizeof id);
+            NB_NCCL(api.GroupStart());
+            for (int l = 0; l < sim->local_gpus; l++) {
+                NB_CUDA(cudaSetDevice(first_dev + l));
+                NB_NCCL(api.CommInitRank(&sim->shards[l].comm, S, id, sim->shards[l].global_index));
+            }
+            NB_NCCL(api.GroupEnd());
+        }
+    }
+    NB_CUDA(cudaSetDevice(first_dev));
+    return sim;
+}
+
+static void destroy_pipeline(SimPipeline *sim) {
+    if (!sim) return;
+    for (Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaStreamSynchronize(sh.stream));
+        NB_CUDA(cudaStreamSynchronize(sh.comm_stream));
+        if (sh.comm) NB_NCCL(nccl().CommDestroy(sh.comm));
+        cudaFree(sh.aos); cudaFree(sh.src_xy[0]); cudaFree(sh.src_xy[1]); cudaFree(sh.src_gm);
+        cudaFree(sh.pos); cudaFree(sh.vel); cudaFree(sh.acc); cudaFree(sh.radius);
+        cudaFree(sh.part); cudaFree(sh.tile_cnt); cudaFree(sh.scratch64);
+        cudaEventDestroy(sh.ev_begin); cudaEventDestroy(sh.ev_end); cudaEventDestroy(sh.ev_massive);
+        cudaEventDestroy(sh.ev_comm); cudaEventDestroy(sh.ev_step);
+        if (sh.own_stream) cudaStreamDestroy(sh.stream);
+        cudaStreamDestroy(sh.comm_stream);
+    }
+    if (!sim->shards.empty()) cudaSetDevice(sim->shards[0].device);
+    delete sim;
+}
+
+}  // namespace nb
+
+/* ---- upload / download ----------------------------------------------------------------- */
+
+namespace nb {
+
+static void sync_all(SimPipeline *sim) {
+    for (Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaStreamSynchronize(sh.stream));
+        NB_CUDA(cudaStreamSynchronize(sh.comm_stream));
+    }
+    NB_CUDA(cudaSetDevice(sim->shards[0].device));
+}
+
+/* Every GPU receives the whole AoS array and derives its SoA state from it. */
+static void upload(SimPipeline *sim, const Particle *ps) {
+    const uint32_t N = sim->data.total_len, M = sim->data.mass_len;
+    const Plan &pl = sim->plan;
+    for (Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaMemcpyAsync(sh.aos, ps, (size_t)N * sizeof(Particle), cudaMemcpyHostToDevice, sh.stream));
+        unpack_targets_kernel<<<ceil_div(N, 256), 256, 0, sh.stream>>>(sh.aos, N, sh.pos, sh.vel, sh.acc, sh.radius);
+        unpack_sources_kernel<<<ceil_div(pl.src_packs_pad, 128), 128, 0, sh.stream>>>(sh.aos, M, pl.src_packs_pad,
+                                                                                    sh.src_xy[0], sh.src_xy[1], sh.src_gm);
+        NB_CUDA(cudaGetLastError());
+        sim->kernels_launched += 2;
+    }
+    sim->cur = 0;
+    sim->has_data = true;
+    sync_all(sim); /* PS may be pageable and reused by the caller right after we return */
+}
+
+/* Patch pos/vel/acc of the ranges a GPU owns into its AoS copy. */
+static void pack_own_ranges(SimPipeline *sim, Shard &sh) {
+    const uint32_t N = sim->data.total_len;
+    uint32_t lo, hi;
+    const uint32_t t0[2] = {sh.a0, sh.b0}, t1[2] = {sh.a1, sh.b1};
+    for (int r = 0; r < 2; r++) {
+        particle_range_of_tiles(sim, t0[r], t1[r], N, &lo, &hi);
+        if (hi <= lo) continue;
+        pack_targets_kernel<<<ceil_div(hi - lo, 256), 256, 0, sh.stream>>>(sh.aos, lo, hi, sh.pos, sh.vel, sh.acc);
+        NB_CUDA(cudaGetLastError());
+        sim->kernels_launched++;
+    }
+}
+
+static void download(SimPipeline *sim, Particle *ps) {
+    const uint32_t N = sim->data.total_len;
+    NB_ASSERT(sim->has_data, "GetSimulationData before SetSimulationData");
+    for (Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        pack_own_ranges(sim, sh);
+    }
+    if (sim->world > 1) {
+        /* other processes own some ranges: all-gather the AoS ranges (32 B = 8 floats per particle) */
+        NcclApi &api = nccl();
+        NB_NCCL(api.GroupStart());
+        for (Shard &sh : sim->shards) {
+            for (int q = 0; q < sim->total_shards; q++) {
+                uint32_t lo, hi;
+                const uint32_t t0[2] = {sim->all_a0[q], sim->all_b0[q]}, t1[2] = {sim->all_a1[q], sim->all_b1[q]};
+                for (int r = 0; r < 2; r++) {
+                    particle_range_of_tiles(sim, t0[r], t1[r], N, &lo, &hi);
+                    if (hi <= lo) continue;
+                    NB_NCCL(api.Broadcast(sh.aos + lo, sh.aos + lo, (size_t)(hi - lo) * 8, kNcclFloat, q, sh.comm, sh.stream));
+                }
+            }
+        }
+        NB_NCCL(api.GroupEnd());
+        Shard &sh = sim->shards[0];
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaMemcpyAsync(ps, sh.aos, (size_t)N * sizeof(Particle), cudaMemcpyDeviceToHost, sh.stream));
+    } else {
+        for (Shard &sh : sim->shards) {
+            NB_CUDA(cudaSetDevice(sh.device));
+            uint32_t lo, hi;
+            const uint32_t t0[2] = {sh.a0, sh.b0}, t1[2] = {sh.a1, sh.b1};
+            for (int r = 0; r < 2; r++) {
+                particle_range_of_tiles(sim, t0[r], t1[r], N, &lo, &hi);
+                if (hi <= lo) continue;
+                NB_CUDA(cudaMemcpyAsync(ps + lo, sh.aos + lo, (size_t)(hi - lo) * sizeof(Particle),
+                                        cudaMemcpyDeviceToHost, sh.stream));
+            }
+        }
+    }
+    sync_all(sim);
+}
+
+}  // namespace nb
+
+/* ---- stepping ------------------------------------------------------------------------------ */
+
+namespace nb {
+
+static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
+    const Plan &pl = sim->plan;
+    Shard &sh = sim->shards[l];
+    const int cur = sim->cur, nxt = cur ^ 1;
+    memset(p, 0, sizeof *p);
+    p->src_xy = sh.src_xy[cur];
+    p->src_gm = sh.src_gm;
+    p->dst_xy[0] = reinterpret_cast<float *>(sh.src_xy[nxt]);
+    p->ndst = 1;
+    if (sim->exchange == kExchangePeerStore) {
+        for (int o = 0; o < sim->local_gpus; o++)
+            if (o != l) p->dst_xy[p->ndst++] = reinterpret_cast<float *>(sim->shards[o].src_xy[nxt]);
+    }
+    p->pos = sh.pos; p->vel = sh.vel; p->acc = sh.acc; p->radius = sh.radius;
+    p->part = sh.part; p->tile_cnt = sh.tile_cnt;
+    p->total_len = sim->data.total_len; p->mass_len = sim->data.mass_len;
+    p->n_pad = pl.n_pad; p->src_packs_pad = pl.src_packs_pad;
+    p->slab_packs = pl.slab_packs; p->nslab = pl.nslab;
+    p->dt = dt;
+}
+
+static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
+    if (t1 <= t0) return;
+    p.tile_first = t0;
+    sim->plan.var->launch((t1 - t0) * sim->plan.nslab, sh.stream, p);
+    NB_CUDA(cudaGetLastError());
+    sim->kernels_launched++;
+}
+
+/* Re-replicate the new massive positions (buffer `nxt`) with NCCL: every shard broadcasts its range. */
+static void exchange_nccl(SimPipeline *sim, int nxt, bool on_comm_stream) {
+    NcclApi &api = nccl();
+    const uint32_t M = sim->data.mass_len;
+    NB_NCCL(api.GroupStart());
+    for (Shard &sh : sim->shards) {
+        float *buf = reinterpret_cast<float *>(sh.src_xy[nxt]);
+        for (int q = 0; q < sim->total_shards; q++) {
+            uint32_t lo, hi;
+            particle_range_of_tiles(sim, sim->all_a0[q], sim->all_a1[q], M, &lo, &hi);
+            if (hi <= lo) continue;
+            const size_t p0 = lo / 4, p1 = ceil_div(hi, 4); /* tile is a multiple of 4: lo is pack aligned */
+            NB_NCCL(api.Broadcast(buf + p0 * 8, buf + p0 * 8, (p1 - p0) * 8, kNcclFloat, q, sh.comm,
+                                  on_comm_stream ? sh.comm_stream : sh.stream));
+        }
+    }
+    NB_NCCL(api.GroupEnd());
+}
+
+static void step_async(SimPipeline *sim, uint32_t n, float dt) {
+    NB_ASSERT(sim->has_data, "PerformSimUpdate before SetSimulationData (ref sim_gpu.h:34)");
+    const int L = sim->local_gpus;
+    for (Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaEventRecord(sh.ev_begin, sh.stream));
+    }
+    const bool split = sim->exchange == kExchangeNccl && sim->overlap;
+    for (uint32_t it = 0; it < n; it++) {
+        const int nxt = sim->cur ^ 1;
+        for (int l = 0; l < L; l++) {
+            Shard &sh = sim->shards[l];
+            NB_CUDA(cudaSetDevice(sh.device));
+            StepParams p;
+            fill_params(sim, l, dt, &p);
+            if (sh.a1 == sh.b0 && !split) {
+                launch_tiles(sim, sh, p, sh.a0, sh.b1); /* one contiguous launch */
+            } else {
+                launch_tiles(sim, sh, p, sh.a0, sh.a1); /* massive targets first: they feed the exchange */
+                if (split) {
+                    NB_CUDA(cudaEventRecord(sh.ev_massive, sh.stream));
+                    NB_CUDA(cudaStreamWaitEvent(sh.comm_stream, sh.ev_massive, 0));
+                }
+                launch_tiles(sim, sh, p, sh.b0, sh.b1); /* massless targets overlap the exchange */
+            }
+        }
+        if (sim->exchange == kExchangeNccl) {
+            exchange_nccl(sim, nxt, split);
+            if (split) {
+                for (Shard &sh : sim->shards) {
+                    NB_CUDA(cudaSetDevice(sh.device));
+                    NB_CUDA(cudaEventRecord(sh.ev_comm, sh.comm_stream));
+                    NB_CUDA(cudaStreamWaitEvent(sh.stream, sh.ev_comm, 0));
+                }
+            }
+        } else if (sim->exchange == kExchangePeerStore) {
+            /* positions were stored into every peer by the epilogue; the next step of each GPU
+             * must wait until all GPUs finished this one */
+            for (Shard &sh : sim->shards) {
+                NB_CUDA(cudaSetDevice(sh.device));
+                NB_CUDA(cudaEventRecord(sh.ev_step, sh.stream));
+            }
+            for (int l = 0; l < L; l++) {
+                NB_CUDA(cudaSetDevice(sim->shards[l].device));
+                for (int o = 0; o < L; o++)
+                    if (o != l) NB_CUDA(cudaStreamWaitEvent(sim->shards[l].stream, sim->shards[o].ev_step, 0));
+            }
+        }
+        sim->cur = nxt;
+    }
+    for (Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaEventRecord(sh.ev_end, sh.stream));
+    }
+    sim->timed = true;
+    NB_CUDA(cudaSetDevice(sim->shards[0].device));
+}
+
+}  // namespace nb
+
+/* ---- C ABI (include/nbody_sim.h) -------------------------------------------------------- */
+
+extern "C" {
+
+SimPipeline *CreateSimPipeline(WorldData data) { return nb::create_pipeline(data, nullptr); }
+
+SimPipeline *NbSimCreate(WorldData data, const NbSimConfig *cfg) { return nb::create_pipeline(data, cfg); }
+
+void DestroySimPipeline(SimPipeline *sim) { nb::destroy_pipeline(sim); }
+
+void SetSimulationData(SimPipeline *sim, const Particle *ps) { nb::upload(sim, ps); }
+
+void GetSimulationData(const SimPipeline *sim, Particle *ps) { nb::download(const_cast<SimPipeline *>(sim), ps); }
+
+void PerformSimUpdate(SimPipeline *sim, uint32_t n, float dt) {
+    if (n == 0) return;
+    nb::step_async(sim, n, dt);
+    nb::sync_all(sim); /* synchronous like the reference's fence wait, ref sim_gpu.c:352-353 */
+}
+
+void NbSimStepAsync(SimPipeline *sim, uint32_t n, float dt) {
+    if (n == 0) return;
+    nb::step_async(sim, n, dt);
+}
+
+void NbSimSynchronize(SimPipeline *sim) { nb::sync_all(sim); }
+
+float NbSimLastStepMs(SimPipeline *sim) {
+    if (!sim->timed) return 0.f;
+    float worst = 0.f;
+    for (nb::Shard &sh : sim->shards) {
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaEventSynchronize(sh.ev_end));
+        float ms = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&ms, sh.ev_begin, sh.ev_end));
+        worst = ms > worst ? ms : worst;
+    }
+    NB_CUDA(cudaSetDevice(sim->shards[0].device));
+    return worst;
+}
+
+void NbSimGetUniqueId(void *out) {
+    nb::NcclUniqueId id;
+    NB_NCCL(nb::nccl().GetUniqueId(&id));
+    memcpy(out, &id, NB_SIM_UNIQUE_ID_BYTES);
+}
+
+void *NbSimHostAlloc(size_t bytes) {
+    void *p = nullptr;
+    NB_CUDA(cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable));
+    return p;
+}
+
+void NbSimHostFree(void *p) {
+    if (p) NB_CUDA(cudaFreeHost(p));
+}
+
+int32_t NbSimDeviceCount(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
+    memset(out, 0, sizeof *out);
+    strncpy(out->device_name, sim->prop.name, sizeof out->device_name - 1);
+    out->device = sim->shards[0].device;
+    out->local_gpus = sim->local_gpus;
+    out->rank = sim->rank;
+    out->world = sim->world;
+    out->sm_count = sim->prop.multiProcessorCount;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, sim->shards[0].device);
+    out->sm_clock_khz = khz;
+    out->cc_major = sim->prop.major;
+    out->cc_minor = sim->prop.minor;
+    out->total_len = sim->data.total_len;
+    out->mass_len = sim->data.mass_len;
+    out->tile_targets = sim->plan.tile;
+    out->threads = sim->plan.var->threads;
+    out->slab_len = sim->plan.slab_packs * 4;
+    out->slabs = sim->plan.nslab;
+    uint32_t tiles = 0;
+    for (const nb::Shard &sh : sim->shards) tiles += (sh.a1 - sh.a0) + (sh.b1 - sh.b0);
+    out->tiles_local = tiles;
+    out->kernels_launched = sim->kernels_launched;
+    out->pairs_per_step = (uint64_t)sim->data.total_len * sim->data.mass_len;
+}
+
+void NbSimDiagnostics(SimPipeline *sim, double *out7) {
+    /* bring one full AoS copy up to date on the host side of the API, then reduce on GPU 0 */
+    const uint32_t N = sim->data.total_len;
+    nb::Shard &sh = sim->shards[0];
+    if (sim->total_shards > 1) {
+        Particle *tmp = (Particle *)NbSimHostAlloc((size_t)N * sizeof(Particle));
+        nb::download(sim, tmp);
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaMemcpyAsync(sh.aos, tmp, (size_t)N * sizeof(Particle), cudaMemcpyHostToDevice, sh.stream));
+        NB_CUDA(cudaStreamSynchronize(sh.stream));
+        NbSimHostFree(tmp);
+    } else {
+        NB_CUDA(cudaSetDevice(sh.device));
+        nb::pack_own_ranges(sim, sh);
+    }
+    NB_CUDA(cudaMemsetAsync(sh.scratch64, 0, 7 * sizeof(double), sh.stream));
+    nb::diagnostics_kernel<<<nb::ceil_div(N, 256), 256, 0, sh.stream>>>(sh.aos, N, sim->data.mass_len, sh.scratch64);
+    NB_CUDA(cudaGetLastError());
+    sim->kernels_launched++;
+    NB_CUDA(cudaMemcpyAsync(out7, sh.scratch64, 7 * sizeof(double), cudaMemcpyDeviceToHost, sh.stream));
+    NB_CUDA(cudaStreamSynchronize(sh.stream));
+}
+
+void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out) {
+    NB_ASSERT(first <= last && last <= sim->data.total_len, "bad target range [%u, %u)", first, last);
+    NB_ASSERT(sim->total_shards == 1, "NbSimAccF64 is a single-GPU diagnostic");
+    if (first == last) return;
+    nb::Shard &sh = sim->shards[0];
+    NB_CUDA(cudaSetDevice(sh.device));
+    double *d = nb::dev_alloc<double>(2 * (size_t)(last - first));
+    nb::acc_f64_kernel<<<nb::ceil_div(last - first, 128), 128, 0, sh.stream>>>(
+        sh.pos, sh.radius, sh.src_xy[sim->cur], sh.src_gm, sim->data.mass_len, first, last, d);
+    NB_CUDA(cudaGetLastError());
+    sim->kernels_launched++;
+    NB_CUDA(cudaMemcpyAsync(out, d, 2 * (size_t)(last - first) * sizeof(double), cudaMemcpyDeviceToHost, sh.stream));
+    NB_CUDA(cudaStreamSynchronize(sh.stream));
+    NB_CUDA(cudaFree(d));
+}
+
+} /* extern "C" */

@@ -1,0 +1,156 @@
+/*
+ * step_kernel.cuh -- the __global__ entry of the hot path (see force_kernel.cuh for the design).
+ *
+ * grid  = (target tiles of this launch) * nslab, slab index fastest so that the CTAs that
+ *         share a target tile are co-resident and its last ticket is drawn early;
+ * block = THREADS threads, T targets per thread, target i = tile*THREADS*T + k*THREADS + tid;
+ * smem  = NS stages of TJP packs (48 B per pack) + 2*NS mbarriers.
+ */
+#pragma once
+
+#include "force_kernel.cuh"
+
+namespace nb {
+
+template <int TJP, int NS>
+constexpr size_t step_smem_bytes() {
+    return (size_t)NS * TJP * 48 + 2 * NS * sizeof(uint64_t) + 16;
+}
+
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+__global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_constant__ StepParams p) {
+    static_assert(TJP % UNR == 0, "tile must be a multiple of the unroll");
+    constexpr int PF = NS - 2;          /* tiles in flight ahead of the consumer */
+    constexpr int NWARP = THREADS / 32;
+    static_assert(PF >= 1, "need at least 3 stages");
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float4 *st_xy = reinterpret_cast<float4 *>(smem_raw);                 /* [NS][TJP][2] */
+    float4 *st_gm = st_xy + (size_t)NS * TJP * 2;                         /* [NS][TJP]    */
+    uint64_t *full = reinterpret_cast<uint64_t *>(st_gm + (size_t)NS * TJP);
+    uint64_t *empty = full + NS;
+    __shared__ int s_last;
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t slab = blockIdx.x % p.nslab;
+    const uint32_t tile = p.tile_first + blockIdx.x / p.nslab;
+    const uint32_t i0 = tile * (THREADS * T) + tid;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < NS; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], NWARP);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+
+    /* targets -> registers (negated, duplicated into both halves of an f32x2) */
+    float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
+#pragma unroll
+    for (int k = 0; k < T; k++) {
+        const uint32_t i = i0 + k * THREADS;
+        float2 x = make_float2(0.f, 0.f);
+        float r = 1.f;
+        if (i < p.total_len) {
+            x = p.pos[i];
+            r = p.radius[i];
+        }
+        ntx[k] = make_float2(-x.x, -x.x);
+        nty[k] = make_float2(-x.y, -x.y);
+        rho[k] = make_float2(r, r);
+        ax[k] = make_float2(0.f, 0.f);
+        ay[k] = make_float2(0.f, 0.f);
+    }
+    __syncthreads();
+
+    /* this CTA's slab, in packs */
+    const uint32_t pk0 = slab * p.slab_packs;
+    const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
+    const uint32_t npk = pk1 > pk0 ? pk1 - pk0 : 0;
+    const uint32_t ntile = (npk + TJP - 1) / TJP;
+
+    auto issue = [&](uint32_t k) { /* thread 0 only: fetch source tile k into stage k % NS */
+        const uint32_t s = k % NS;
+        const uint32_t f = k / NS;
+        if (f > 0) mbar_wait(&empty[s], (f - 1) & 1);
+        const uint32_t first = pk0 + k * TJP;
+        const uint32_t cnt = min((uint32_t)TJP, pk1 - first);
+        mbar_expect_tx(&full[s], cnt * 48u);
+        bulk_g2s(st_xy + (size_t)s * TJP * 2, p.src_xy + (size_t)first * 2, cnt * 32u, &full[s]);
+        bulk_g2s(st_gm + (size_t)s * TJP, p.src_gm + first, cnt * 16u, &full[s]);
+    };
+
+    if (tid == 0) {
+        for (uint32_t k = 0; k < (uint32_t)PF && k < ntile; k++) issue(k);
+    }
+
+    for (uint32_t k = 0; k < ntile; k++) {
+        if (tid == 0 && k + PF < ntile) issue(k + PF);
+        const uint32_t s = k % NS;
+        mbar_wait(&full[s], (k / NS) & 1);
+
+        const float4 *xy = st_xy + (size_t)s * TJP * 2;
+        const float4 *gm = st_gm + (size_t)s * TJP;
+        const uint32_t cnt = min((uint32_t)TJP, npk - k * TJP);
+#pragma unroll 1
+        for (uint32_t q = 0; q < cnt; q += UNR) {
+#pragma unroll
+            for (int u = 0; u < UNR; u++) {
+                const float4 xs = xy[2 * (q + u)];
+                const float4 ys = xy[2 * (q + u) + 1];
+                const float4 gs = gm[q + u];
+                interact_pack<T>(xs, ys, gs, ntx, nty, rho, ax, ay);
+            }
+        }
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+    }
+
+    /* slab partial of each target: even-source half + odd-source half */
+    float2 a[T];
+#pragma unroll
+    for (int k = 0; k < T; k++) a[k] = make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+
+    if (p.nslab == 1) {
+#pragma unroll
+        for (int k = 0; k < T; k++) {
+            const uint32_t i = i0 + k * THREADS;
+            if (i < p.total_len) integrate_store(p, i, a[k]);
+        }
+        return;
+    }
+
+#pragma unroll
+    for (int k = 0; k < T; k++) {
+        const uint32_t i = i0 + k * THREADS;
+        __stcg(&p.part[(size_t)slab * p.n_pad + i], a[k]);
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned ticket = atomicAdd(&p.tile_cnt[tile], 1u);
+        const int last = (ticket == p.nslab - 1);
+        if (last) p.tile_cnt[tile] = 0; /* ready for the next step */
+        s_last = last;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    /* last CTA of this target tile: add the slab partials in slab order and integrate */
+#pragma unroll
+    for (int k = 0; k < T; k++) {
+        const uint32_t i = i0 + k * THREADS;
+        if (i >= p.total_len) continue;
+        float2 sum = __ldcg(&p.part[i]);
+        for (uint32_t s = 1; s < p.nslab; s++) {
+            const float2 v = __ldcg(&p.part[(size_t)s * p.n_pad + i]);
+            sum.x = __fadd_rn(sum.x, v.x);
+            sum.y = __fadd_rn(sum.y, v.y);
+        }
+        integrate_store(p, i, sum);
+    }
+}
+
+}  // namespace nb

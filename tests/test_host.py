@@ -1,0 +1,153 @@
+"""CPU-side tests of the product library (no GPU needed): the partition permutation, the galaxy
+generator, UpdateWorld_CPU, and that libnbody.so exports every symbol the headers declare."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from _oracle import PARTICLE, RefLib, mass_len_of
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+# The seven cases of the reference's only unit test (ref test/test_particle_sort.c:27-111):
+# input -> (expected order, expected count of non-zeros).
+SORT_CASES = [
+    ([1, 2, 3, 4, 5], [1, 2, 3, 4, 5], 5),       # test_on_non_zeros
+    ([0, 0, 0, 0, 0], [0, 0, 0, 0, 0], 0),       # test_on_zeros
+    ([1, 2, 3, 0, 0], [1, 2, 3, 0, 0], 3),       # test_on_sorted
+    ([0, 0, 1, 2, 3], [3, 2, 1, 0, 0], 3),       # test_on_reverse_sorted_odd
+    ([0, 0, 0, 1, 2, 3], [3, 2, 1, 0, 0, 0], 3),  # test_on_reverse_sorted_even
+    ([0, 1, 2, 0, 3], [3, 1, 2, 0, 0], 3),       # test_on_unsorted_odd
+    ([0, 1, 2, 0, 3, 0], [3, 1, 2, 0, 0, 0], 3),  # test_on_unsorted_even
+]
+
+
+def _particles_from_masses(ms):
+    ps = np.zeros(len(ms), dtype=PARTICLE)
+    ps["mass"] = ms
+    ps["px"] = np.arange(len(ms)) + 1000.0   # identity tag that survives the partition
+    ps["radius"] = 1.0
+    return ps
+
+
+@pytest.mark.parametrize("inp,exp,count", SORT_CASES)
+def test_oracle_partition_int_reference_cases(oracle, inp, exp, count):
+    out, m = oracle.partition_int(inp)
+    assert m == count and out.tolist() == exp
+
+
+@pytest.mark.parametrize("inp,exp,count", SORT_CASES)
+def test_createworld_partition_reference_cases(nb, inp, exp, count):
+    """The same seven cases through the product's CreateWorld + GetWorldParticles."""
+    with nb.World(_particles_from_masses(inp)) as w:
+        got = w.particles()
+        assert w.mass_len == count
+    assert got["mass"].tolist() == [float(x) for x in exp]
+
+
+def test_createworld_partition_random_matches_oracle(nb, oracle):
+    rng = np.random.default_rng(7)
+    for n in (1, 2, 3, 17, 256, 1001):
+        ms = rng.integers(0, 3, size=n).astype(np.float32) * rng.random(n).astype(np.float32)
+        ms[rng.random(n) < 0.1] = -1.0       # negative mass counts as massless (mass <= 0)
+        ps = _particles_from_masses(ms)
+        exp, m = oracle.partition(ps)
+        with nb.World(ps) as w:
+            got = w.particles()
+            assert w.mass_len == m
+        assert got.tobytes() == exp.tobytes()
+
+
+def test_createworld_copies_and_size_query(nb):
+    ps = _particles_from_masses([1, 0, 2])
+    before = ps.copy()
+    with nb.World(ps) as w:
+        ps["px"] = -1.0                       # caller keeps ownership; World must not alias it
+        got = w.particles()
+    assert sorted(got["px"].tolist()) == sorted(before["px"].tolist())
+    # size pointer may be NULL (ref world.c:93)
+    L = nb.lib()
+    w = nb.CreateWorld(before)
+    assert L.GetWorldParticles(w, None)
+    nb.DestroyWorld(w)
+    nb.DestroyWorld(None)                     # NULL is ignored (ref world.c:68)
+
+
+@pytest.mark.parametrize("name", ["galaxy_1000_2.npz", "galaxy_4003_2.npz", "galaxy_6000_3.npz"])
+def test_make_galaxies_bit_identical_to_reference_fixture(nb, golden, name):
+    g = golden(name)
+    n = len(g["input"])
+    gal = int(name.split("_")[2].split(".")[0])
+    mine = nb.make_galaxies(n, gal, seed=int(g["seed"]))
+    assert mine.tobytes() == g["input"].tobytes()
+
+
+@pytest.mark.parametrize("n,gal,seed", [(200, 2, 1), (777, 3, 99), (20000, 2, 11037), (5000, 5, 3)])
+def test_make_galaxies_bit_identical_to_compiled_reference(nb, n, gal, seed):
+    if not RefLib.available("avx"):
+        pytest.skip("oracle/_ref not built")
+    r = RefLib("avx")
+    assert nb.make_galaxies(n, gal, seed=seed).tobytes() == r.make_galaxies(n, gal, seed=seed).tobytes()
+
+
+def test_make_galaxies_value_ranges(nb):
+    ps = nb.make_galaxies(16384, 2)
+    massless = ps["mass"] == 0
+    assert 0.4 < massless.mean() < 0.6                     # about half are tracer particles
+    assert np.all(ps["radius"][massless] == 0.5)
+    assert np.all(ps["radius"] > 0)                        # softening never zero
+    cores = ps["radius"] >= 200
+    assert cores.sum() == 2
+
+
+@pytest.mark.parametrize("name", ["galaxy_1000_2.npz", "galaxy_4003_2.npz"])
+def test_update_world_cpu_matches_reference_fixture(nb, golden, name):
+    """UpdateWorld_CPU of the product rounds like the reference's AVX build."""
+    g = golden(name)
+    with nb.World(g["input"]) as w:
+        w.update_cpu(float(g["dt"]), 1)
+        one = w.particles()
+        w.update_cpu(float(g["dt"]), 9)
+        ten = w.particles()
+    assert one.tobytes() == g["step1"].tobytes()
+    assert ten.tobytes() == g["step10"].tobytes()
+
+
+def test_update_world_cpu_zero_steps_is_noop(nb, golden):
+    g = golden("galaxy_1000_2.npz")
+    with nb.World(g["input"]) as w:
+        w.update_cpu(0.01, 0)
+        assert w.particles().tobytes() == g["world0"].tobytes()
+
+
+def _declared_functions(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = re.findall(r"^\s*(?:const\s+)?[A-Za-z_][A-Za-z0-9_ ]*?[\s\*]+([A-Z][A-Za-z0-9_]+)\s*\([^;{]*\)\s*;", text,
+                       flags=re.M)
+    return [n for n in names if not n.startswith("V2")]
+
+
+def test_library_exports_every_declared_symbol(nb):
+    declared = _declared_functions("nbody.h") + _declared_functions("galaxy.h") + _declared_functions("nbody_sim.h")
+    for must in ("CreateWorld", "UpdateWorld_GPU", "MakeGalaxies", "CreateSimPipeline", "PerformSimUpdate",
+                 "NbSimCreate", "NbSimGetUniqueId"):
+        assert must in declared, (must, declared)
+    L = C.CDLL(nb.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/ but not exported by libnbody.so"
+
+
+def test_library_is_sm100a_only(nb):
+    out = subprocess.run(["cuobjdump", "-lelf", nb.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    archs = set(re.findall(r"sm_\d+a?", out.stdout))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_device_count_without_gpu_is_zero_or_more(nb):
+    assert nb.device_count() >= 0

@@ -1,0 +1,329 @@
+/*
+ * tools/tune.cu -- measurement harness for the hot kernel (development tool, not product).
+ *
+ *   tune pipes              FP32 / MUFU pipe micro-benchmarks (what the roofline rests on)
+ *   tune sweep [N] [M]      time every compiled step_kernel variant on random particles
+ *
+ * Numbers are CUDA-event times after warm-up; the effective SM clock is derived in-kernel from
+ * clock64() against %globaltimer so that fractions of peak can be quoted at the clock that was
+ * actually running.
+ */
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "step_kernel.cuh"
+#include "util.cuh"
+
+using namespace nb;
+
+/* ------------------------------------------------------------------------------------------ */
+/* pipe micro-benchmarks                                                                        */
+
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+struct ClockRec {
+    unsigned long long cycles, ns;
+};
+
+/* MODE 0: FFMA (scalar) x ILP chains; 1: FFMA2; 2: MUFU.RSQ; 3: mix 9 packed FP32 : 2 MUFU (the
+ * kernel's ratio); 4: FFMA2 + FMUL2 + FADD2 mix 4:3:2 without MUFU */
+template <int MODE>
+__global__ void __launch_bounds__(256) pipe_kernel(float *out, int iters, ClockRec *rec) {
+    float2 a[8], b, c;
+    for (int k = 0; k < 8; k++) a[k] = make_float2(threadIdx.x * 0.001f + k, threadIdx.x * 0.002f - k);
+    b = make_float2(1.0001f, 0.9999f);
+    c = make_float2(0.0001f, -0.0001f);
+    const unsigned long long t0 = gtimer();
+    const long long c0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            if (MODE == 0) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    a[k].x = fmaf(a[k].x, b.x, c.x);
+                    a[k].y = fmaf(a[k].y, b.y, c.y);
+                }
+            } else if (MODE == 1) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(a[k], b, c);
+            } else if (MODE == 2) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    a[k].x = rsqrt_mufu(a[k].x);
+                    a[k].y = rsqrt_mufu(a[k].y);
+                }
+            } else if (MODE == 3) {
+                /* per chain pair: 9 packed + 2 MUFU, four independent chains */
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    float2 dx = __fadd2_rn(a[k], b);
+                    float2 dy = __fadd2_rn(a[k + 4], c);
+                    float2 r2 = __ffma2_rn(dy, dy, b);
+                    r2 = __ffma2_rn(dx, dx, r2);
+                    float2 inv;
+                    inv.x = rsqrt_mufu(r2.x);
+                    inv.y = rsqrt_mufu(r2.y);
+                    float2 i2 = __fmul2_rn(inv, inv);
+                    float2 gi = __fmul2_rn(c, inv);
+                    float2 f = __fmul2_rn(i2, gi);
+                    a[k] = __ffma2_rn(dx, f, a[k]);
+                    a[k + 4] = __ffma2_rn(dy, f, a[k + 4]);
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    float2 dx = __fadd2_rn(a[k], b);
+                    float2 dy = __fadd2_rn(a[k + 4], c);
+                    float2 r2 = __ffma2_rn(dy, dy, b);
+                    r2 = __ffma2_rn(dx, dx, r2);
+                    float2 i2 = __fmul2_rn(r2, r2);
+                    float2 gi = __fmul2_rn(c, r2);
+                    float2 f = __fmul2_rn(i2, gi);
+                    a[k] = __ffma2_rn(dx, f, a[k]);
+                    a[k + 4] = __ffma2_rn(dy, f, a[k + 4]);
+                }
+            }
+        }
+    }
+    const long long c1 = clock64();
+    const unsigned long long t1 = gtimer();
+    float s = 0.f;
+    for (int k = 0; k < 8; k++) s += a[k].x + a[k].y;
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0) {
+        rec[blockIdx.x].cycles = (unsigned long long)(c1 - c0);
+        rec[blockIdx.x].ns = t1 - t0;
+    }
+}
+
+template <int MODE>
+static void run_pipe(const char *name, double ops_per_iter_per_thread, const char *unit, int sms, int ctas_per_sm) {
+    const int grid = sms * ctas_per_sm, block = 256, iters = 20000;
+    float *out;
+    ClockRec *rec;
+    NB_CUDA(cudaMalloc(&out, (size_t)grid * block * sizeof(float)));
+    NB_CUDA(cudaMalloc(&rec, (size_t)grid * sizeof(ClockRec)));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    pipe_kernel<MODE><<<grid, block>>>(out, 2000, rec);
+    NB_CUDA(cudaDeviceSynchronize());
+    float best = 1e30f;
+    for (int r = 0; r < 3; r++) {
+        cudaEventRecord(e0);
+        pipe_kernel<MODE><<<grid, block>>>(out, iters, rec);
+        cudaEventRecord(e1);
+        NB_CUDA(cudaDeviceSynchronize());
+        float ms;
+        cudaEventElapsedTime(&ms, e0, e1);
+        best = std::min(best, ms);
+    }
+    std::vector<ClockRec> h(grid);
+    NB_CUDA(cudaMemcpy(h.data(), rec, grid * sizeof(ClockRec), cudaMemcpyDeviceToHost));
+    double cyc = 0, ns = 0;
+    for (auto &r : h) {
+        cyc += r.cycles;
+        ns += r.ns;
+    }
+    const double mhz = cyc / ns * 1e3;
+    const double total = ops_per_iter_per_thread * iters * (double)grid * block;
+    const double per_clk_sm = total / (cyc / grid) / sms; /* ops per SM clock per SM */
+    printf("  %-34s ctas/sm %d  %8.3f ms  %9.2f G%s/s  %7.2f %s/clk/SM  (SM clock %.0f MHz)\n", name, ctas_per_sm, best,
+           total / best * 1e-6, unit, per_clk_sm, unit, mhz);
+    cudaFree(out);
+    cudaFree(rec);
+}
+
+static void pipes(int sms) {
+    printf("pipe micro-benchmarks (256 threads/CTA):\n");
+    for (int c : {2, 4, 8}) {
+        run_pipe<0>("FFMA scalar (fma lanes)", 4 * 16.0, "fma", sms, c);
+        run_pipe<1>("FFMA2 packed (fma lanes)", 4 * 16.0, "fma", sms, c);
+        run_pipe<2>("MUFU.RSQ", 4 * 16.0, "rsq", sms, c);
+        run_pipe<4>("FP32 mix 4 FFMA2:3 FMUL2:2 FADD2 (pairs)", 4 * 8.0, "pair", sms, c);
+        run_pipe<3>("kernel mix 9 packed + 2 MUFU (pairs)", 4 * 8.0, "pair", sms, c);
+    }
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* step_kernel variant sweep                                                                    */
+
+struct Buffers {
+    float4 *src_xy[2], *src_gm;
+    float2 *pos, *vel, *acc, *part;
+    float *radius;
+    unsigned *cnt;
+    uint32_t N, M, src_packs, src_packs_pad;
+    size_t part_elems;
+};
+
+static float frand() { return (float)rand() / (float)RAND_MAX; }
+
+static Buffers make_buffers(uint32_t N, uint32_t M) {
+    Buffers b;
+    b.N = N;
+    b.M = M;
+    b.src_packs = (M + 3) / 4;
+    b.src_packs_pad = (b.src_packs + 255) / 256 * 256;
+    std::vector<float> xy((size_t)b.src_packs_pad * 8), gm((size_t)b.src_packs_pad * 4);
+    std::vector<float2> pos(N), vel(N);
+    std::vector<float> rad(N);
+    for (uint32_t i = 0; i < N; i++) {
+        pos[i] = make_float2((frand() - 0.5f) * 2e5f, (frand() - 0.5f) * 2e5f);
+        vel[i] = make_float2(0.f, 0.f);
+        rad[i] = 0.5f + frand() * 9.f;
+    }
+    for (uint32_t j = 0; j < b.src_packs_pad * 4; j++) {
+        const uint32_t o = (j >> 2) * 8 + (j & 3);
+        if (j < M) {
+            xy[o] = pos[j].x;
+            xy[o + 4] = pos[j].y;
+            gm[j] = 10.f * (100.f + frand() * 1e4f);
+        } else {
+            xy[o] = kPadPos;
+            xy[o + 4] = kPadPos;
+            gm[j] = 0.f;
+        }
+    }
+    NB_CUDA(cudaMalloc(&b.src_xy[0], xy.size() * 4));
+    NB_CUDA(cudaMalloc(&b.src_xy[1], xy.size() * 4));
+    NB_CUDA(cudaMalloc(&b.src_gm, gm.size() * 4));
+    NB_CUDA(cudaMalloc(&b.pos, N * sizeof(float2)));
+    NB_CUDA(cudaMalloc(&b.vel, N * sizeof(float2)));
+    NB_CUDA(cudaMalloc(&b.acc, N * sizeof(float2)));
+    NB_CUDA(cudaMalloc(&b.radius, N * sizeof(float)));
+    b.part_elems = (size_t)512 * (N + 4096);
+    NB_CUDA(cudaMalloc(&b.part, b.part_elems * sizeof(float2)));
+    NB_CUDA(cudaMalloc(&b.cnt, (N / 64 + 16) * sizeof(unsigned)));
+    NB_CUDA(cudaMemset(b.cnt, 0, (N / 64 + 16) * sizeof(unsigned)));
+    NB_CUDA(cudaMemcpy(b.src_xy[0], xy.data(), xy.size() * 4, cudaMemcpyHostToDevice));
+    NB_CUDA(cudaMemcpy(b.src_xy[1], xy.data(), xy.size() * 4, cudaMemcpyHostToDevice));
+    NB_CUDA(cudaMemcpy(b.src_gm, gm.data(), gm.size() * 4, cudaMemcpyHostToDevice));
+    NB_CUDA(cudaMemcpy(b.pos, pos.data(), N * sizeof(float2), cudaMemcpyHostToDevice));
+    NB_CUDA(cudaMemcpy(b.vel, vel.data(), N * sizeof(float2), cudaMemcpyHostToDevice));
+    NB_CUDA(cudaMemcpy(b.radius, rad.data(), N * sizeof(float), cudaMemcpyHostToDevice));
+    return b;
+}
+
+static double g_peak_pairs = 0; /* FP32-pipe ceiling in pairs/s at max clock: SMs*128*clk/9 */
+static double g_peak_flops = 0;
+
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
+    auto kern = step_kernel<THREADS, T, TJP, NS, MINB, UNR>;
+    const size_t smem = step_smem_bytes<TJP, NS>();
+    NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, smem));
+    cudaFuncAttributes fa;
+    NB_CUDA(cudaFuncGetAttributes(&fa, kern));
+    const uint32_t tile = THREADS * T;
+    const uint32_t ntiles = (b.N + tile - 1) / tile;
+    uint32_t slab_packs = ((b.src_packs + nslab_req - 1) / nslab_req + 3) / 4 * 4;
+    uint32_t nslab = (b.src_packs + slab_packs - 1) / slab_packs;
+    if ((size_t)nslab * ntiles * tile > b.part_elems) {
+        printf("  (skip: partial buffer too small)\n");
+        return;
+    }
+    StepParams p;
+    memset(&p, 0, sizeof p);
+    p.src_xy = b.src_xy[0];
+    p.src_gm = b.src_gm;
+    p.dst_xy[0] = (float *)b.src_xy[1];
+    p.ndst = 1;
+    p.pos = b.pos; p.vel = b.vel; p.acc = b.acc; p.radius = b.radius;
+    p.part = b.part; p.tile_cnt = b.cnt;
+    p.total_len = b.N; p.mass_len = b.M;
+    p.n_pad = ntiles * tile;
+    p.src_packs_pad = (b.src_packs + TJP - 1) / TJP * TJP;
+    p.slab_packs = slab_packs; p.nslab = nslab;
+    p.tile_first = 0;
+    p.dt = 0.f; /* dt = 0: positions stay put, every repetition does identical work */
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const uint32_t grid = ntiles * nslab;
+    for (int w = 0; w < 2; w++) kern<<<grid, THREADS, smem>>>(p);
+    NB_CUDA(cudaDeviceSynchronize());
+    float best = 1e30f, sum = 0.f;
+    const int reps = 5;
+    for (int r = 0; r < reps; r++) {
+        cudaEventRecord(e0);
+        kern<<<grid, THREADS, smem>>>(p);
+        cudaEventRecord(e1);
+        NB_CUDA(cudaDeviceSynchronize());
+        float ms;
+        cudaEventElapsedTime(&ms, e0, e1);
+        best = std::min(best, ms);
+        sum += ms;
+    }
+    const double pairs = (double)b.N * b.M;
+    const double rate = pairs / (best * 1e-3);
+    const double waves = (double)grid / (occ * sms);
+    printf("  t%dx%d tjp%d ns%d unr%d minb%d | regs %3d occ %d | nslab %4u grid %6u waves %7.2f | best %8.3f ms avg %8.3f | "
+           "%7.1f Gpairs/s  %5.1f%% of FP32 peak (14 flop/pair)  %5.1f%% of 9-slot ceiling\n",
+           THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
+           100.0 * rate * 14.0 / g_peak_flops, 100.0 * rate / g_peak_pairs);
+    fflush(stdout);
+}
+
+static void sweep(uint32_t N, uint32_t M, int sms) {
+    printf("variant sweep: N = %u targets, M = %u sources, %.3e pairs/step\n", N, M, (double)N * M);
+    Buffers b = make_buffers(N, M);
+    const uint32_t base = std::max(1u, (uint32_t)(24.0 * sms * 2 / ((N + 1023) / 1024)));
+    for (uint32_t ns : {base, base * 2}) {
+        run_variant<256, 4, 128, 4, 2, 2>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 2, 1>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 2, 4>(b, ns, sms);
+        run_variant<256, 4, 256, 3, 2, 2>(b, ns, sms);
+        run_variant<256, 4, 64, 6, 2, 2>(b, ns, sms);
+        run_variant<128, 4, 128, 4, 4, 2>(b, ns, sms);
+        run_variant<128, 4, 128, 4, 3, 2>(b, ns, sms);
+        run_variant<512, 4, 128, 4, 1, 2>(b, ns, sms);
+        run_variant<256, 2, 128, 4, 3, 2>(b, ns, sms);
+        run_variant<256, 2, 128, 4, 4, 2>(b, ns, sms);
+        run_variant<128, 2, 64, 4, 6, 2>(b, ns, sms);
+        run_variant<128, 8, 128, 4, 2, 1>(b, ns, sms);
+        run_variant<256, 8, 128, 4, 1, 1>(b, ns, sms);
+        run_variant<64, 4, 64, 4, 8, 2>(b, ns, sms);
+        run_variant<256, 1, 128, 4, 4, 4>(b, ns, sms);
+        run_variant<256, 3, 128, 4, 2, 2>(b, ns, sms);
+        run_variant<256, 6, 128, 4, 1, 1>(b, ns, sms);
+        run_variant<384, 4, 128, 4, 1, 2>(b, ns, sms);
+    }
+}
+
+int main(int argc, char **argv) {
+    int dev = 0;
+    NB_CUDA(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    NB_CUDA(cudaGetDeviceProperties(&prop, dev));
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+    const int sms = prop.multiProcessorCount;
+    g_peak_flops = (double)sms * 128 * 2 * khz * 1e3;
+    g_peak_pairs = (double)sms * 128 * khz * 1e3 / 9.0;
+    printf("device %s, %d SMs, max SM clock %d MHz, FP32 peak %.2f TFLOP/s, 9-slot ceiling %.1f Gpairs/s\n", prop.name, sms,
+           khz / 1000, g_peak_flops * 1e-12, g_peak_pairs * 1e-9);
+    const char *cmd = argc > 1 ? argv[1] : "pipes";
+    if (!strcmp(cmd, "pipes")) pipes(sms);
+    else if (!strcmp(cmd, "sweep")) {
+        const uint32_t N = argc > 2 ? (uint32_t)atol(argv[2]) : 262144;
+        const uint32_t M = argc > 3 ? (uint32_t)atol(argv[3]) : N / 2;
+        sweep(N, M, sms);
+    } else {
+        fprintf(stderr, "usage: tune pipes | sweep [N] [M]\n");
+        return 2;
+    }
+    return 0;
+}

@@ -30,7 +30,11 @@ def _report(tag, cuda_ref, ref_f64, cuda_f64):
         print(f"   {name:12s} median {s['median']:.2e}  p99 {s['p99']:.2e}  max {s['max']:.2e}")
 
 
-def _check_one_step(nb, oracle, w0, ref1, dt, tag):
+def _check_one_step(nb, oracle, w0, ref1, dt, tag, strict=True):
+    """strict=True: the north_star bound itself (N <= ~20K, where the reference's own FP32 noise is
+    below it).  strict=False (larger N): the reference's rounding noise against FP64 exceeds 1e-5
+    (BASELINE.md section 2), so the bound on CUDA-vs-reference is the reference's own distance to FP64
+    (triangle inequality) and the 1e-5 bound is asserted on CUDA-vs-FP64 instead."""
     m = mass_len_of(w0)
     with nb.World(w0) as w:          # w0 is already partitioned: CreateWorld keeps its order
         assert w.mass_len == m
@@ -41,8 +45,13 @@ def _check_one_step(nb, oracle, w0, ref1, dt, tag):
     ref_f64 = rel_acc_error(acc_of(ref1), truth)
     cuda_f64 = rel_acc_error(acc_of(got), truth)
     _report(tag, cuda_ref, ref_f64, cuda_f64)
-    assert np.percentile(cuda_ref, 99) <= TOL_ACC
-    assert cuda_ref.max() <= TOL_ACC_WORST
+    if strict:
+        assert np.percentile(cuda_ref, 99) <= TOL_ACC
+        assert cuda_ref.max() <= TOL_ACC_WORST
+    else:
+        assert np.percentile(cuda_f64, 99) <= TOL_ACC
+        assert np.percentile(cuda_ref, 99) <= 1.1 * np.percentile(ref_f64, 99) + 2e-6
+        assert np.median(cuda_ref) <= 1.1 * np.median(ref_f64) + 1e-6
     assert np.percentile(cuda_f64, 99) <= max(np.percentile(ref_f64, 99), 2e-6) * 1.05
     assert cuda_f64.max() <= max(ref_f64.max(), 1e-5) * 1.05
     # integrator: v = v0 + a dt, x = x0 + v dt with the reference's rounding, given OUR acc
@@ -67,7 +76,7 @@ def test_one_step_against_oracle(nb, oracle, n, gal):
     ps = nb.make_galaxies(n, gal)
     w0, m = oracle.partition(ps)
     ref1 = oracle.update(w0, m, 0.01, 1, 8)   # bit-exact restatement of the reference AVX build
-    _check_one_step(nb, oracle, w0, ref1, 0.01, f"galaxy {n}/{gal}")
+    _check_one_step(nb, oracle, w0, ref1, 0.01, f"galaxy {n}/{gal}", strict=n <= 20000)
 
 
 @pytest.mark.parametrize("name", ["galaxy_1000_2.npz", "galaxy_4003_2.npz"])

@@ -107,8 +107,58 @@ __device__ __forceinline__ float rsqrt_mufu(float x) {
     return r;
 }
 
+/*
+ * Instruction forms of the pair arithmetic (same operations, same rounding, same summation order --
+ * results are bit-identical between forms; only the SASS differs):
+ *   kFormPacked      everything as f32x2 (FADD2/FFMA2/FMUL2)
+ *   kFormScalarAcc   packed up to f, the two accumulate FMAs as four scalar FFMA: an FFMA2 that reads
+ *                    three distinct register pairs (dx, f, acc) costs the SM sub-partition three
+ *                    dispatch cycles instead of two (tools/tune.cu `pipes`)
+ *   kFormScalar      everything scalar
+ */
+enum { kFormPacked = 0, kFormTargetPacked = 1, kFormScalarAcc = 2, kFormScalar = 3 };
+
+template <int FORM>
+__device__ __forceinline__ void interact_two(const float2 x, const float2 y, const float2 g, const float2 ntx,
+                                             const float2 nty, const float2 rho, float2 &ax, float2 &ay) {
+    if constexpr (FORM == kFormScalar) {
+        const float dx0 = __fadd_rn(x.x, ntx.x), dx1 = __fadd_rn(x.y, ntx.y);
+        const float dy0 = __fadd_rn(y.x, nty.x), dy1 = __fadd_rn(y.y, nty.y);
+        float r20 = __fmaf_rn(dy0, dy0, rho.x), r21 = __fmaf_rn(dy1, dy1, rho.y);
+        r20 = __fmaf_rn(dx0, dx0, r20);
+        r21 = __fmaf_rn(dx1, dx1, r21);
+        const float i0 = rsqrt_mufu(r20), i1 = rsqrt_mufu(r21);
+        const float f0 = __fmul_rn(__fmul_rn(i0, i0), __fmul_rn(g.x, i0));
+        const float f1 = __fmul_rn(__fmul_rn(i1, i1), __fmul_rn(g.y, i1));
+        ax.x = __fmaf_rn(dx0, f0, ax.x);
+        ax.y = __fmaf_rn(dx1, f1, ax.y);
+        ay.x = __fmaf_rn(dy0, f0, ay.x);
+        ay.y = __fmaf_rn(dy1, f1, ay.y);
+    } else {
+        const float2 dx = __fadd2_rn(x, ntx);
+        const float2 dy = __fadd2_rn(y, nty);
+        float2 r2 = __ffma2_rn(dy, dy, rho);
+        r2 = __ffma2_rn(dx, dx, r2);
+        float2 inv;
+        inv.x = rsqrt_mufu(r2.x);
+        inv.y = rsqrt_mufu(r2.y);
+        const float2 inv2 = __fmul2_rn(inv, inv);
+        const float2 gi = __fmul2_rn(g, inv);
+        const float2 f = __fmul2_rn(inv2, gi);
+        if constexpr (FORM == kFormScalarAcc) {
+            ax.x = __fmaf_rn(dx.x, f.x, ax.x);
+            ax.y = __fmaf_rn(dx.y, f.y, ax.y);
+            ay.x = __fmaf_rn(dy.x, f.x, ay.x);
+            ay.y = __fmaf_rn(dy.y, f.y, ay.y);
+        } else {
+            ax = __ffma2_rn(dx, f, ax);
+            ay = __ffma2_rn(dy, f, ay);
+        }
+    }
+}
+
 /* 4 sources (one pack) against T register-resident targets. */
-template <int T>
+template <int T, int FORM = kFormPacked>
 __device__ __forceinline__ void interact_pack(const float4 xs, const float4 ys, const float4 gs,
                                               const float2 (&ntx)[T], const float2 (&nty)[T],
                                               const float2 (&rho)[T], float2 (&ax)[T], float2 (&ay)[T]) {
@@ -117,34 +167,32 @@ __device__ __forceinline__ void interact_pack(const float4 xs, const float4 ys, 
     const float2 g01 = make_float2(gs.x, gs.y), g23 = make_float2(gs.z, gs.w);
 #pragma unroll
     for (int t = 0; t < T; t++) {
-        {
-            const float2 dx = __fadd2_rn(x01, ntx[t]);
-            const float2 dy = __fadd2_rn(y01, nty[t]);
-            float2 r2 = __ffma2_rn(dy, dy, rho[t]);
-            r2 = __ffma2_rn(dx, dx, r2);
-            float2 inv;
-            inv.x = rsqrt_mufu(r2.x);
-            inv.y = rsqrt_mufu(r2.y);
-            const float2 inv2 = __fmul2_rn(inv, inv);
-            const float2 gi = __fmul2_rn(g01, inv);
-            const float2 f = __fmul2_rn(inv2, gi);
-            ax[t] = __ffma2_rn(dx, f, ax[t]);
-            ay[t] = __ffma2_rn(dy, f, ay[t]);
-        }
-        {
-            const float2 dx = __fadd2_rn(x23, ntx[t]);
-            const float2 dy = __fadd2_rn(y23, nty[t]);
-            float2 r2 = __ffma2_rn(dy, dy, rho[t]);
-            r2 = __ffma2_rn(dx, dx, r2);
-            float2 inv;
-            inv.x = rsqrt_mufu(r2.x);
-            inv.y = rsqrt_mufu(r2.y);
-            const float2 inv2 = __fmul2_rn(inv, inv);
-            const float2 gi = __fmul2_rn(g23, inv);
-            const float2 f = __fmul2_rn(inv2, gi);
-            ax[t] = __ffma2_rn(dx, f, ax[t]);
-            ay[t] = __ffma2_rn(dy, f, ay[t]);
-        }
+        interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+        interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+    }
+}
+
+/*
+ * Target-packed form: an f32x2 holds TWO targets against ONE source (the source is a warp-uniform
+ * scalar operand).  Same 9 packed instructions + 2 MUFU per two pairs, but one accumulator pair per
+ * two targets (half the accumulator registers of the source-packed form, so more targets fit per
+ * thread and every LDS.128 of sources feeds twice as many pairs) and each target sums its sources
+ * in plain source order.
+ */
+template <int T2>
+__device__ __forceinline__ void interact_pack_tp(const float4 xs, const float4 ys, const float4 gs,
+                                                 const float2 (&ntx)[T2], const float2 (&nty)[T2],
+                                                 const float2 (&rho)[T2], float2 (&ax)[T2], float2 (&ay)[T2]) {
+    const float sx[4] = {xs.x, xs.y, xs.z, xs.w};
+    const float sy[4] = {ys.x, ys.y, ys.z, ys.w};
+    const float sg[4] = {gs.x, gs.y, gs.z, gs.w};
+#pragma unroll
+    for (int l = 0; l < 4; l++) {
+        const float2 x2 = make_float2(sx[l], sx[l]);
+        const float2 y2 = make_float2(sy[l], sy[l]);
+        const float2 g2 = make_float2(sg[l], sg[l]);
+#pragma unroll
+        for (int t = 0; t < T2; t++) interact_two<kFormPacked>(x2, y2, g2, ntx[t], nty[t], rho[t], ax[t], ay[t]);
     }
 }
 

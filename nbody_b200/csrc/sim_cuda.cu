@@ -27,31 +27,31 @@ namespace nb {
 
 struct Variant {
     const char *name;
-    int threads, T, tjp, ns, unr;
+    int threads, T, tjp, ns, minb, unr;
     size_t smem;
     const void *func;
     void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p);
 };
 
-template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM>
 static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p) {
-    step_kernel<THREADS, T, TJP, NS, MINB, UNR><<<grid, THREADS, step_smem_bytes<TJP, NS>(), st>>>(p);
+    step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM><<<grid, THREADS, step_smem_bytes<TJP, NS>(), st>>>(p);
 }
 
-#define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR)                                              \
+#define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR, FORM)                                        \
     {                                                                                                 \
-        NAME, THREADS, T, TJP, NS, UNR, step_smem_bytes<TJP, NS>(),                                   \
-            (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR>,                                \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR>                                            \
+        NAME, THREADS, T, TJP, NS, MINB, UNR, step_smem_bytes<TJP, NS>(),                             \
+            (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>                                      \
     }
 
 static const Variant kVariants[] = {
-    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2), /* default for large N: 1024 targets per CTA */
-    NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2), /* 512 targets per CTA                        */
-    NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2),  /* 256 targets per CTA, small N               */
-    NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2),
-    NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1),
-    NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2),    /* 256 targets per CTA, 2 warps               */
+    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2, kFormPacked), /* default for large N: 1024 targets per CTA */
+    NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2, kFormPacked), /* 512 targets per CTA                        */
+    NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2, kFormPacked),  /* 256 targets per CTA, small N               */
+    NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked),
+    NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked),
+    NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2, kFormPacked),    /* 256 targets per CTA, 2 warps               */
 };
 static const int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 

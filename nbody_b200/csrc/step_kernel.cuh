@@ -17,8 +17,11 @@ constexpr size_t step_smem_bytes() {
     return (size_t)NS * TJP * 48 + 2 * NS * sizeof(uint64_t) + 16;
 }
 
-template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM = kFormPacked>
 __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_constant__ StepParams p) {
+    constexpr bool TP = FORM == kFormTargetPacked;
+    static_assert(!TP || T % 2 == 0, "the target-packed form needs an even number of targets per thread");
+    constexpr int TR = TP ? T / 2 : T; /* f32x2 register sets per thread */
     static_assert(TJP % UNR == 0, "tile must be a multiple of the unroll");
     constexpr int PF = NS - 2;          /* tiles in flight ahead of the consumer */
     constexpr int NWARP = THREADS / 32;
@@ -45,20 +48,32 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
 
-    /* targets -> registers (negated, duplicated into both halves of an f32x2) */
-    float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
+    /* targets -> registers, negated.  Source-packed: one target duplicated into both halves of an
+     * f32x2; target-packed: targets 2k and 2k+1 of this thread side by side. */
+    float2 ntx[TR], nty[TR], rho[TR], ax[TR], ay[TR];
 #pragma unroll
-    for (int k = 0; k < T; k++) {
-        const uint32_t i = i0 + k * THREADS;
-        float2 x = make_float2(0.f, 0.f);
-        float r = 1.f;
-        if (i < p.total_len) {
-            x = p.pos[i];
-            r = p.radius[i];
+    for (int k = 0; k < TR; k++) {
+        float2 x[2];
+        float r[2];
+#pragma unroll
+        for (int h = 0; h < (TP ? 2 : 1); h++) {
+            const uint32_t i = i0 + (TP ? 2 * k + h : k) * THREADS;
+            x[h] = make_float2(0.f, 0.f);
+            r[h] = 1.f;
+            if (i < p.total_len) {
+                x[h] = p.pos[i];
+                r[h] = p.radius[i];
+            }
         }
-        ntx[k] = make_float2(-x.x, -x.x);
-        nty[k] = make_float2(-x.y, -x.y);
-        rho[k] = make_float2(r, r);
+        if constexpr (TP) {
+            ntx[k] = make_float2(-x[0].x, -x[1].x);
+            nty[k] = make_float2(-x[0].y, -x[1].y);
+            rho[k] = make_float2(r[0], r[1]);
+        } else {
+            ntx[k] = make_float2(-x[0].x, -x[0].x);
+            nty[k] = make_float2(-x[0].y, -x[0].y);
+            rho[k] = make_float2(r[0], r[0]);
+        }
         ax[k] = make_float2(0.f, 0.f);
         ay[k] = make_float2(0.f, 0.f);
     }
@@ -100,17 +115,26 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
                 const float4 xs = xy[2 * (q + u)];
                 const float4 ys = xy[2 * (q + u) + 1];
                 const float4 gs = gm[q + u];
-                interact_pack<T>(xs, ys, gs, ntx, nty, rho, ax, ay);
+                if constexpr (TP) interact_pack_tp<TR>(xs, ys, gs, ntx, nty, rho, ax, ay);
+                else interact_pack<TR, FORM>(xs, ys, gs, ntx, nty, rho, ax, ay);
             }
         }
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
     }
 
-    /* slab partial of each target: even-source half + odd-source half */
+    /* slab partial of each target.  Source-packed: even-source half + odd-source half;
+     * target-packed: the two halves are two targets. */
     float2 a[T];
 #pragma unroll
-    for (int k = 0; k < T; k++) a[k] = make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+    for (int k = 0; k < TR; k++) {
+        if constexpr (TP) {
+            a[2 * k] = make_float2(ax[k].x, ay[k].x);
+            a[2 * k + 1] = make_float2(ax[k].y, ay[k].y);
+        } else {
+            a[k] = make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+        }
+    }
 
     if (p.nslab == 1) {
 #pragma unroll

@@ -202,6 +202,17 @@ def test_ragged_sizes_against_oracle(nb, oracle, n):
         w.update_gpu(0.01, 1)
         got = w.particles()
     assert np.array_equal(got["mass"], w0["mass"])
+    # Random clouds contain targets whose acceleration is a near-complete cancellation of large
+    # terms; for those the relative error of ANY FP32 evaluation is unbounded.  So: the 1e-5 bound
+    # on the 99th percentile, and for every particle the error normalised by sum_j |term_ij| (the
+    # conditioning-free scale the oracle reports) within a few FP32 ulps.
+    truth, nrm = oracle.acc_f64(w0, m)
     err = rel_acc_error(acc_of(got), acc_of(ref))
-    assert err.max() <= 2e-5, err.max()
+    if n >= 100:
+        assert np.percentile(err, 99) <= 1e-5, np.percentile(err, 99)
+    d = np.hypot(*(acc_of(got).astype(np.float64) - truth).T)
+    d_ref = np.hypot(*(acc_of(ref).astype(np.float64) - truth).T)
+    scale = np.where(nrm > 0, nrm, 1.0)
+    assert (d / scale).max() <= 1e-6, (d / scale).max()
+    assert (d / scale).max() <= max(3.0 * (d_ref / scale).max(), 5e-7)
     assert np.allclose(got["px"], ref["px"], rtol=1e-6, atol=1e-6)

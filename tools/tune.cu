@@ -37,8 +37,13 @@ struct ClockRec {
  * kernel's ratio); 4: FFMA2 + FMUL2 + FADD2 mix 4:3:2 without MUFU */
 template <int MODE>
 __global__ void __launch_bounds__(256) pipe_kernel(float *out, int iters, ClockRec *rec) {
-    float2 a[8], b, c;
+    float2 a[8], b, c, bb[8], cc[8];
     for (int k = 0; k < 8; k++) a[k] = make_float2(threadIdx.x * 0.001f + k, threadIdx.x * 0.002f - k);
+    for (int k = 0; k < 8; k++) {
+        bb[k] = make_float2(1.0f + 1e-6f * (threadIdx.x + k), 1.0f - 1e-6f * (threadIdx.x + k));
+        cc[k] = make_float2(1e-5f * (threadIdx.x - k), -1e-5f * (threadIdx.x + 2 * k));
+    }
+    unsigned ia = threadIdx.x, ib = blockIdx.x;
     b = make_float2(1.0001f, 0.9999f);
     c = make_float2(0.0001f, -0.0001f);
     const unsigned long long t0 = gtimer();
@@ -62,6 +67,63 @@ __global__ void __launch_bounds__(256) pipe_kernel(float *out, int iters, ClockR
                     a[k].x = rsqrt_mufu(a[k].x);
                     a[k].y = rsqrt_mufu(a[k].y);
                 }
+            } else if (MODE == 5) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __fmul2_rn(a[k], b);
+            } else if (MODE == 6) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __fadd2_rn(a[k], c);
+            } else if (MODE == 7) {
+                /* three distinct register pairs per instruction, nothing for the reuse cache */
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(a[k], bb[k], cc[k]);
+            } else if (MODE == 8) {
+                /* two distinct pairs + one shared */
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(a[k], bb[k], c);
+            } else if (MODE == 12) {
+                /* scalar FFMA, three distinct registers */
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    a[k].x = fmaf(a[k].x, bb[k].x, cc[k].x);
+                    a[k].y = fmaf(a[k].y, bb[k].y, cc[k].y);
+                }
+            } else if (MODE == 13) {
+                /* the kernel's accumulate pair: two FFMA2 sharing one operand (3 + 2 distinct pairs) */
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    a[k] = __ffma2_rn(bb[k], cc[k], a[k]);
+                    a[k + 4] = __ffma2_rn(bb[k + 4], cc[k], a[k + 4]);
+                }
+            } else if (MODE == 14) {
+                /* same work as four scalar FFMA */
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    a[k].x = fmaf(bb[k].x, cc[k].x, a[k].x);
+                    a[k].y = fmaf(bb[k].y, cc[k].y, a[k].y);
+                    a[k + 4].x = fmaf(bb[k + 4].x, cc[k].x, a[k + 4].x);
+                    a[k + 4].y = fmaf(bb[k + 4].y, cc[k].y, a[k + 4].y);
+                }
+            } else if (MODE == 9) {
+                /* 8 FFMA2 + 2 independent MUFU: does a MUFU issue cost the FMA pipe a cycle? */
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(a[k], b, c);
+                cc[0].x = rsqrt_mufu(cc[0].x);
+                cc[1].x = rsqrt_mufu(cc[1].x);
+            } else if (MODE == 10) {
+                /* 8 FFMA2 + 2 independent integer ALU ops */
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(a[k], b, c);
+                ia = (ia ^ (ia >> 3)) + 0x9e3779b9u;
+                ib = (ib ^ (ib << 5)) + 0x7f4a7c15u;
+            } else if (MODE == 11) {
+                /* 8 FFMA2 + 4 MUFU */
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(a[k], b, c);
+                cc[0].x = rsqrt_mufu(cc[0].x);
+                cc[1].x = rsqrt_mufu(cc[1].x);
+                cc[2].x = rsqrt_mufu(cc[2].x);
+                cc[3].x = rsqrt_mufu(cc[3].x);
             } else if (MODE == 3) {
                 /* per chain pair: 9 packed + 2 MUFU, four independent chains */
 #pragma unroll
@@ -99,6 +161,9 @@ __global__ void __launch_bounds__(256) pipe_kernel(float *out, int iters, ClockR
     const unsigned long long t1 = gtimer();
     float s = 0.f;
     for (int k = 0; k < 8; k++) s += a[k].x + a[k].y;
+    if (MODE >= 7)
+        for (int k = 0; k < 8; k++) s += bb[k].x * cc[k].y + cc[k].x;
+    s += (float)(ia + ib);
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
     if (threadIdx.x == 0) {
         rec[blockIdx.x].cycles = (unsigned long long)(c1 - c0);
@@ -137,7 +202,7 @@ static void run_pipe(const char *name, double ops_per_iter_per_thread, const cha
     }
     const double mhz = cyc / ns * 1e3;
     const double total = ops_per_iter_per_thread * iters * (double)grid * block;
-    const double per_clk_sm = total / (cyc / grid) / sms; /* ops per SM clock per SM */
+    const double per_clk_sm = total / (best * 1e-3 * mhz * 1e6) / sms; /* ops per SM clock per SM */
     printf("  %-34s ctas/sm %d  %8.3f ms  %9.2f G%s/s  %7.2f %s/clk/SM  (SM clock %.0f MHz)\n", name, ctas_per_sm, best,
            total / best * 1e-6, unit, per_clk_sm, unit, mhz);
     cudaFree(out);
@@ -146,9 +211,19 @@ static void run_pipe(const char *name, double ops_per_iter_per_thread, const cha
 
 static void pipes(int sms) {
     printf("pipe micro-benchmarks (256 threads/CTA):\n");
-    for (int c : {2, 4, 8}) {
+    for (int c : {2, 8}) {
         run_pipe<0>("FFMA scalar (fma lanes)", 4 * 16.0, "fma", sms, c);
         run_pipe<1>("FFMA2 packed (fma lanes)", 4 * 16.0, "fma", sms, c);
+        run_pipe<5>("FMUL2 packed (lanes)", 4 * 16.0, "mul", sms, c);
+        run_pipe<6>("FADD2 packed (lanes)", 4 * 16.0, "add", sms, c);
+        run_pipe<7>("FFMA2, 3 distinct register pairs", 4 * 16.0, "fma", sms, c);
+        run_pipe<8>("FFMA2, 2 distinct pairs + 1 shared", 4 * 16.0, "fma", sms, c);
+        run_pipe<12>("FFMA scalar, 3 distinct registers", 4 * 16.0, "fma", sms, c);
+        run_pipe<13>("FFMA2 pairs sharing one operand", 4 * 16.0, "fma", sms, c);
+        run_pipe<14>("same as scalar FFMA x4", 4 * 16.0, "fma", sms, c);
+        run_pipe<9>("8 FFMA2 + 2 MUFU (fma lanes)", 4 * 16.0, "fma", sms, c);
+        run_pipe<11>("8 FFMA2 + 4 MUFU (fma lanes)", 4 * 16.0, "fma", sms, c);
+        run_pipe<10>("8 FFMA2 + 2 int ALU (fma lanes)", 4 * 16.0, "fma", sms, c);
         run_pipe<2>("MUFU.RSQ", 4 * 16.0, "rsq", sms, c);
         run_pipe<4>("FP32 mix 4 FFMA2:3 FMUL2:2 FADD2 (pairs)", 4 * 8.0, "pair", sms, c);
         run_pipe<3>("kernel mix 9 packed + 2 MUFU (pairs)", 4 * 8.0, "pair", sms, c);
@@ -218,9 +293,9 @@ static Buffers make_buffers(uint32_t N, uint32_t M) {
 static double g_peak_pairs = 0; /* FP32-pipe ceiling in pairs/s at max clock: SMs*128*clk/9 */
 static double g_peak_flops = 0;
 
-template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM = 0>
 static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
-    auto kern = step_kernel<THREADS, T, TJP, NS, MINB, UNR>;
+    auto kern = step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>;
     const size_t smem = step_smem_bytes<TJP, NS>();
     NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
@@ -270,9 +345,9 @@ static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
     const double pairs = (double)b.N * b.M;
     const double rate = pairs / (best * 1e-3);
     const double waves = (double)grid / (occ * sms);
-    printf("  t%dx%d tjp%d ns%d unr%d minb%d | regs %3d occ %d | nslab %4u grid %6u waves %7.2f | best %8.3f ms avg %8.3f | "
+    printf("  %s t%dx%d tjp%d ns%d unr%d minb%d | regs %3d occ %d | nslab %4u grid %6u waves %7.2f | best %8.3f ms avg %8.3f | "
            "%7.1f Gpairs/s  %5.1f%% of FP32 peak (14 flop/pair)  %5.1f%% of 9-slot ceiling\n",
-           THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
+           FORM == 0 ? "packed" : FORM == 1 ? "tgtpack" : FORM == 2 ? "sclacc" : "scalar", THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
            100.0 * rate * 14.0 / g_peak_flops, 100.0 * rate / g_peak_pairs);
     fflush(stdout);
 }
@@ -281,25 +356,35 @@ static void sweep(uint32_t N, uint32_t M, int sms) {
     printf("variant sweep: N = %u targets, M = %u sources, %.3e pairs/step\n", N, M, (double)N * M);
     Buffers b = make_buffers(N, M);
     const uint32_t base = std::max(1u, (uint32_t)(24.0 * sms * 2 / ((N + 1023) / 1024)));
-    for (uint32_t ns : {base, base * 2}) {
+    const char *set = getenv("TUNE_SET");
+    const bool full = set && !strcmp(set, "full");
+    for (uint32_t ns : {base}) {
         run_variant<256, 4, 128, 4, 2, 2>(b, ns, sms);
+        run_variant<512, 4, 128, 4, 1, 2>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 3, 1>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 3, 2>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 2, 2, 2>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 2, 1, 2>(b, ns, sms);
+        run_variant<512, 4, 128, 4, 1, 2, 2>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 3, 1, 2>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 2, 2, 3>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 2, 1, 3>(b, ns, sms);
+        run_variant<512, 4, 128, 4, 1, 2, 3>(b, ns, sms);
+        run_variant<256, 4, 128, 4, 3, 1, 3>(b, ns, sms);
+        run_variant<256, 2, 128, 4, 4, 2, 3>(b, ns, sms);
+        run_variant<256, 8, 128, 4, 1, 1, 3>(b, ns, sms);
+        if (!full) continue;
         run_variant<256, 4, 128, 4, 2, 1>(b, ns, sms);
         run_variant<256, 4, 128, 4, 2, 4>(b, ns, sms);
         run_variant<256, 4, 256, 3, 2, 2>(b, ns, sms);
         run_variant<256, 4, 64, 6, 2, 2>(b, ns, sms);
         run_variant<128, 4, 128, 4, 4, 2>(b, ns, sms);
-        run_variant<128, 4, 128, 4, 3, 2>(b, ns, sms);
-        run_variant<512, 4, 128, 4, 1, 2>(b, ns, sms);
         run_variant<256, 2, 128, 4, 3, 2>(b, ns, sms);
         run_variant<256, 2, 128, 4, 4, 2>(b, ns, sms);
         run_variant<128, 2, 64, 4, 6, 2>(b, ns, sms);
         run_variant<128, 8, 128, 4, 2, 1>(b, ns, sms);
-        run_variant<256, 8, 128, 4, 1, 1>(b, ns, sms);
         run_variant<64, 4, 64, 4, 8, 2>(b, ns, sms);
-        run_variant<256, 1, 128, 4, 4, 4>(b, ns, sms);
         run_variant<256, 3, 128, 4, 2, 2>(b, ns, sms);
-        run_variant<256, 6, 128, 4, 1, 1>(b, ns, sms);
-        run_variant<384, 4, 128, 4, 1, 2>(b, ns, sms);
     }
 }
 

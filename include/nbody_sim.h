@@ -118,6 +118,24 @@ typedef struct NbSimInfo {
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);
 
+/* The work decomposition the pipeline would use for these sizes, computed on the host alone (no
+ * device needed).  TILE_RANGES, when not NULL, receives 4 values per shard q in [0, SHARDS):
+ * massive target tiles [a0, a1) and massless target tiles [b0, b1); a tile is TILE_TARGETS
+ * consecutive particles in World order.  SM_COUNT <= 0 means a B200 (148). */
+typedef struct NbSimPlanInfo {
+    char variant[16];        /* kernel variant name                               */
+    uint32_t threads;        /* threads per CTA                                   */
+    uint32_t tile_targets;   /* targets per tile (= per CTA)                      */
+    uint32_t tiles;          /* ceil(total_len / tile_targets)                    */
+    uint32_t massive_tiles;  /* tiles containing at least one massive particle    */
+    uint32_t slab_len;       /* sources per partial-sum slab                      */
+    uint32_t slabs;          /* slabs per tile; fixes the summation order         */
+    uint32_t ctas_per_sm;    /* resident CTAs per SM the plan assumes             */
+} NbSimPlanInfo;
+
+void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm_count, NbSimPlanInfo *out,
+               uint32_t *tile_ranges);
+
 /* Number of CUDA devices visible to the process (0 when there is no driver/GPU). */
 int32_t NbSimDeviceCount(void);
 

@@ -23,10 +23,11 @@ from .api import (  # noqa: F401
     get_unique_id,
     lib,
     make_galaxies,
+    plan,
 )
 
 __all__ = [
     "PARTICLE", "LIB_PATH", "CreateWorld", "DestroyWorld", "GetWorldParticles", "MakeGalaxies",
     "SimConfig", "SimPipeline", "UpdateWorld_CPU", "UpdateWorld_GPU", "World", "device_count",
-    "get_unique_id", "lib", "make_galaxies",
+    "get_unique_id", "lib", "make_galaxies", "plan",
 ]

@@ -37,6 +37,19 @@ class SimConfig(C.Structure):  # include/nbody_sim.h NbSimConfig
     ]
 
 
+class SimPlanInfo(C.Structure):  # include/nbody_sim.h NbSimPlanInfo
+    _fields_ = [
+        ("variant", C.c_char * 16),
+        ("threads", C.c_uint32),
+        ("tile_targets", C.c_uint32),
+        ("tiles", C.c_uint32),
+        ("massive_tiles", C.c_uint32),
+        ("slab_len", C.c_uint32),
+        ("slabs", C.c_uint32),
+        ("ctas_per_sm", C.c_uint32),
+    ]
+
+
 class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
     _fields_ = [
         ("device_name", C.c_char * 64),
@@ -107,6 +120,7 @@ def lib():
         "NbSimHostFree": (None, [vp]),
         "NbSimGetInfo": (None, [vp, C.POINTER(SimInfo)]),
         "NbSimDeviceCount": (C.c_int32, []),
+        "NbSimPlan": (None, [u32, u32, C.c_int32, C.c_int32, C.POINTER(SimPlanInfo), vp]),
         "NbSimDiagnostics": (None, [vp, vp]),
         "NbSimAccF64": (None, [vp, u32, u32, vp]),
         # world.c extras
@@ -136,6 +150,16 @@ def _view(ptr, n):
         return np.empty(0, dtype=PARTICLE)
     buf = (C.c_uint8 * (n * 32)).from_address(ptr)
     return np.frombuffer(buf, dtype=PARTICLE)
+
+
+def plan(total_len, mass_len, shards=1, sm_count=0):
+    """Host-only work decomposition (NbSimPlan): returns (info dict, [(a0, a1, b0, b1)] per shard)."""
+    info = SimPlanInfo()
+    ranges = np.zeros((shards, 4), dtype=np.uint32)
+    lib().NbSimPlan(total_len, mass_len, shards, sm_count, C.byref(info), ranges.ctypes.data_as(C.c_void_p))
+    d = {name: (getattr(info, name).decode() if name == "variant" else int(getattr(info, name)))
+         for name, _ in info._fields_}
+    return d, [tuple(int(x) for x in r) for r in ranges]
 
 
 def device_count():

@@ -46,7 +46,8 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p) 
     }
 
 static const Variant kVariants[] = {
-    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2, kFormPacked), /* default for large N: 1024 targets per CTA */
+    NB_VARIANT("t512x4", 512, 4, 128, 4, 1, 2, kFormPacked), /* default for large N: 2048 targets per CTA */
+    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2, kFormPacked), /* 1024 targets per CTA                       */
     NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2, kFormPacked), /* 512 targets per CTA                        */
     NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2, kFormPacked),  /* 256 targets per CTA, small N               */
     NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked),
@@ -124,10 +125,12 @@ static const Variant *pick_variant(uint32_t total_len, int sm_count) {
             if (strcmp(e, kVariants[i].name) == 0) return &kVariants[i];
         NB_FAIL("NBODY_VARIANT=%s is not a known kernel variant", e);
     }
-    /* enough 1024-target tiles to give every SM a few: use the big tile, else the small one */
-    if (total_len >= (uint32_t)sm_count * 1024u * 2u) return &kVariants[0];
-    if (total_len >= (uint32_t)sm_count * 256u) return &kVariants[1];
-    return &kVariants[2];
+    /* The biggest tile that still leaves every SM several tiles, also when the World is later
+     * split over 8 GPUs (tile size fixes the summation order, so it must not depend on the GPU count). */
+    if (total_len >= (uint32_t)sm_count * 2048u * 3u) return &kVariants[0];
+    if (total_len >= (uint32_t)sm_count * 1024u) return &kVariants[1];
+    if (total_len >= (uint32_t)sm_count * 256u) return &kVariants[2];
+    return &kVariants[3];
 }
 
 
@@ -191,22 +194,35 @@ static Tp *dev_alloc(size_t count) {
     return p;
 }
 
-static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
-    Plan &pl = sim->plan;
-    const uint32_t N = sim->data.total_len, M = sim->data.mass_len;
-    pl.var = pick_variant(N, sim->prop.multiProcessorCount);
-    NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
-    int occ = 0;
-    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl.var->func, pl.var->threads, pl.var->smem));
-    NB_ASSERT(occ > 0, "kernel variant %s does not fit on this device", pl.var->name);
-    pl.ctas_per_sm = occ;
+/* Geometry from sizes alone -- no device is touched, so the same plan can be computed (and
+ * tested) on a machine without a GPU.  Occupancy is the variant's __launch_bounds__ promise. */
+static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl) {
+    pl.var = pick_variant(N, sm_count);
+    pl.ctas_per_sm = pl.var->minb;
     pl.tile = (uint32_t)pl.var->threads * pl.var->T;
     pl.ntiles = ceil_div(N, pl.tile);
     pl.mtiles = ceil_div(M, pl.tile);
     pl.n_pad = pl.ntiles * pl.tile;
     pl.src_packs = ceil_div(M, 4);
     pl.src_packs_pad = std::max(1u, ceil_div(pl.src_packs, (uint32_t)pl.var->tjp)) * pl.var->tjp;
-    choose_slabs(pl, (uint32_t)occ * sim->prop.multiProcessorCount, forced_slab);
+    choose_slabs(pl, (uint32_t)pl.ctas_per_sm * sm_count, forced_slab);
+}
+
+/* Which tiles shard q of S computes: an equal share of the tiles holding massive particles
+ * (they feed the exchange) and an equal share of the purely massless tiles. */
+static void shard_tiles(const Plan &pl, int S, int q, uint32_t *a0, uint32_t *a1, uint32_t *b0, uint32_t *b1) {
+    split_range(0, pl.mtiles, S, q, a0, a1);
+    split_range(pl.mtiles, pl.ntiles - pl.mtiles, S, q, b0, b1);
+}
+
+static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
+    Plan &pl = sim->plan;
+    plan_host(sim->data.total_len, sim->data.mass_len, sim->prop.multiProcessorCount, forced_slab, pl);
+    NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+    int occ = 0;
+    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl.var->func, pl.var->threads, pl.var->smem));
+    NB_ASSERT(occ >= pl.var->minb, "kernel variant %s: %d CTAs/SM resident, %d planned", pl.var->name, occ,
+              pl.var->minb);
 }
 
 }  // namespace nb
@@ -263,10 +279,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
     /* who computes which tiles */
     const int S = sim->total_shards;
     sim->all_a0.resize(S); sim->all_a1.resize(S); sim->all_b0.resize(S); sim->all_b1.resize(S);
-    for (int q = 0; q < S; q++) {
-        split_range(0, pl.mtiles, S, q, &sim->all_a0[q], &sim->all_a1[q]);
-        split_range(pl.mtiles, pl.ntiles - pl.mtiles, S, q, &sim->all_b0[q], &sim->all_b1[q]);
-    }
+    for (int q = 0; q < S; q++) shard_tiles(pl, S, q, &sim->all_a0[q], &sim->all_a1[q], &sim->all_b0[q], &sim->all_b1[q]);
 
     /* exchange mode */
     if (S == 1) {
@@ -632,6 +645,26 @@ void *NbSimHostAlloc(size_t bytes) {
 
 void NbSimHostFree(void *p) {
     if (p) NB_CUDA(cudaFreeHost(p));
+}
+
+void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm_count, NbSimPlanInfo *out,
+               uint32_t *tile_ranges) {
+    NB_ASSERT(mass_len <= total_len && total_len > 0 && shards >= 1, "bad plan request");
+    nb::Plan pl;
+    nb::plan_host(total_len, mass_len, sm_count > 0 ? sm_count : 148, (uint32_t)nb::env_int("NBODY_SLAB", 0), pl);
+    memset(out, 0, sizeof *out);
+    strncpy(out->variant, pl.var->name, sizeof out->variant - 1);
+    out->threads = pl.var->threads;
+    out->tile_targets = pl.tile;
+    out->tiles = pl.ntiles;
+    out->massive_tiles = pl.mtiles;
+    out->slab_len = pl.slab_packs * 4;
+    out->slabs = pl.nslab;
+    out->ctas_per_sm = pl.ctas_per_sm;
+    if (tile_ranges)
+        for (int q = 0; q < shards; q++)
+            nb::shard_tiles(pl, shards, q, &tile_ranges[4 * q], &tile_ranges[4 * q + 1], &tile_ranges[4 * q + 2],
+                            &tile_ranges[4 * q + 3]);
 }
 
 int32_t NbSimDeviceCount(void) {

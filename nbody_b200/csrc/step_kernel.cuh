@@ -167,11 +167,24 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
     for (int k = 0; k < T; k++) {
         const uint32_t i = i0 + k * THREADS;
         if (i >= p.total_len) continue;
-        float2 sum = __ldcg(&p.part[i]);
-        for (uint32_t s = 1; s < p.nslab; s++) {
-            const float2 v = __ldcg(&p.part[(size_t)s * p.n_pad + i]);
-            sum.x = __fadd_rn(sum.x, v.x);
-            sum.y = __fadd_rn(sum.y, v.y);
+        /* loads of 8 slabs in flight at a time (L2 latency), added strictly in slab order */
+        float2 sum = make_float2(0.f, 0.f);
+        for (uint32_t s0 = 0; s0 < p.nslab; s0 += 8) {
+            float2 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++)
+                if (s0 + u < p.nslab) v[u] = __ldcg(&p.part[(size_t)(s0 + u) * p.n_pad + i]);
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                if (s0 + u < p.nslab) {
+                    if (s0 + u == 0) {
+                        sum = v[0];
+                    } else {
+                        sum.x = __fadd_rn(sum.x, v[u].x);
+                        sum.y = __fadd_rn(sum.y, v[u].y);
+                    }
+                }
+            }
         }
         integrate_store(p, i, sum);
     }

@@ -352,13 +352,33 @@ static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
     fflush(stdout);
 }
 
-static void sweep(uint32_t N, uint32_t M, int sms) {
+static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
     printf("variant sweep: N = %u targets, M = %u sources, %.3e pairs/step\n", N, M, (double)N * M);
     Buffers b = make_buffers(N, M);
     const uint32_t base = std::max(1u, (uint32_t)(24.0 * sms * 2 / ((N + 1023) / 1024)));
     const char *set = getenv("TUNE_SET");
     const bool full = set && !strcmp(set, "full");
-    for (uint32_t ns : {base}) {
+    const bool small = set && !strcmp(set, "small");
+    std::vector<uint32_t> list;
+    if (nslab_list) {
+        for (const char *c = nslab_list; *c;) {
+            list.push_back((uint32_t)strtoul(c, (char **)&c, 10));
+            if (*c == ',') c++;
+        }
+    } else {
+        list.push_back(base);
+    }
+    for (uint32_t ns : list) {
+        if (small) {
+            run_variant<128, 2, 64, 4, 6, 2>(b, ns, sms);
+            run_variant<64, 4, 64, 4, 8, 2>(b, ns, sms);
+            run_variant<128, 4, 128, 4, 4, 2>(b, ns, sms);
+            run_variant<64, 2, 64, 4, 12, 2>(b, ns, sms);
+            run_variant<256, 2, 128, 4, 3, 2>(b, ns, sms);
+            run_variant<256, 4, 128, 4, 2, 2>(b, ns, sms);
+            run_variant<128, 1, 64, 4, 8, 4>(b, ns, sms);
+            continue;
+        }
         run_variant<256, 4, 128, 4, 2, 2>(b, ns, sms);
         run_variant<512, 4, 128, 4, 1, 2>(b, ns, sms);
         run_variant<256, 4, 128, 4, 3, 1>(b, ns, sms);
@@ -405,7 +425,7 @@ int main(int argc, char **argv) {
     else if (!strcmp(cmd, "sweep")) {
         const uint32_t N = argc > 2 ? (uint32_t)atol(argv[2]) : 262144;
         const uint32_t M = argc > 3 ? (uint32_t)atol(argv[3]) : N / 2;
-        sweep(N, M, sms);
+        sweep(N, M, sms, argc > 4 ? argv[4] : nullptr);
     } else {
         fprintf(stderr, "usage: tune pipes | sweep [N] [M]\n");
         return 2;

@@ -274,7 +274,9 @@ def run_ours(args):
                 wld.update_gpu(args.dt, 1)         # H2D (if stale) + step, synchronous
                 wld.particles(copy=False)          # D2H into the World's array
         else:
-            host = arr.copy()
+            pinned = nb.PinnedParticles(len(arr))   # page-locked host buffer, like the World's own array
+            host = pinned.array
+            host[:] = arr
 
             def e2e_step():
                 sim.set_data(host)                 # sim_gpu.h seam: H2D
@@ -307,14 +309,25 @@ def run_ours(args):
 
     peak = fp32_peak_tflops(info) * world
     achieved = value * 1e9 * FLOP_PER_PAIR * 1e-12
+    # DRAM bytes of the dominant kernel per launch come from a committed ncu capture of the same
+    # configuration (profiles/ncu_traffic.json); null when this configuration was never captured.
+    traffic = None
+    try:
+        table = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        key = f"{info['total_len']},{info['mass_len']},{info['threads']}x{info['tile_targets'] // info['threads']},{info['slabs']}"
+        if world == 1 and key in table:
+            traffic = table[key]["bytes"]
+    except (OSError, ValueError):
+        pass
     roofline = {
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-        "traffic": None,
+        "traffic": traffic,
         "peak_source": "derived: SMs x 128 x 2 x max SM clock (MEASURED_PEAKS.json has no FP32 figure)",
         "kernel": f"nb::step_kernel ({info['threads']} threads x {info['tile_targets'] // info['threads']} targets, "
                   f"{info['slabs']} slabs of {info['slab_len']} sources)",
         "flop_per_pair": FLOP_PER_PAIR,
         "ceiling_frac": 14.0 / 18.0,
+        "measured_dispatch_ceiling_frac": 18.0 / 21.4 * 14.0 / 18.0,
     }
     if clocks and clocks.get("sm_mhz"):
         roofline["frac_at_measured_clock"] = achieved / (peak * clocks["sm_mhz"] * 1e3 / info["sm_clock_khz"])

@@ -9,6 +9,7 @@ path here; if libnbody.so is missing, importing the bindings raises.
 """
 from .api import (  # noqa: F401
     PARTICLE,
+    PinnedParticles,
     LIB_PATH,
     CreateWorld,
     DestroyWorld,
@@ -27,7 +28,7 @@ from .api import (  # noqa: F401
 )
 
 __all__ = [
-    "PARTICLE", "LIB_PATH", "CreateWorld", "DestroyWorld", "GetWorldParticles", "MakeGalaxies",
+    "PARTICLE", "PinnedParticles", "LIB_PATH", "CreateWorld", "DestroyWorld", "GetWorldParticles", "MakeGalaxies",
     "SimConfig", "SimPipeline", "UpdateWorld_CPU", "UpdateWorld_GPU", "World", "device_count",
     "get_unique_id", "lib", "make_galaxies", "plan",
 ]

@@ -207,6 +207,27 @@ def make_galaxies(particle_count, galaxy_count, seed=11037):
     return MakeGalaxies(particle_count, galaxy_count)
 
 
+class PinnedParticles:
+    """A Particle array in page-locked host memory (NbSimHostAlloc), so SetSimulationData /
+    GetSimulationData run at link speed.  `.array` is a NumPy view; freed on close()/GC."""
+
+    def __init__(self, n):
+        self._ptr = lib().NbSimHostAlloc(max(n, 1) * 32)
+        self.array = _view(self._ptr, n)
+
+    def close(self):
+        if self._ptr:
+            self.array = None
+            lib().NbSimHostFree(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def get_unique_id():
     buf = (C.c_uint8 * UNIQUE_ID_BYTES)()
     lib().NbSimGetUniqueId(buf)

@@ -30,12 +30,25 @@ struct Variant {
     int threads, T, tjp, ns, minb, unr;
     size_t smem;
     const void *func;
-    void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p);
+    void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl);
 };
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM>
-static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p) {
-    step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM><<<grid, THREADS, step_smem_bytes<TJP, NS>(), st>>>(p);
+static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
+    /* Programmatic dependent launch: the next step's CTAs may become resident while this step's last
+     * CTAs drain; they run their prologue and block in griddepcontrol.wait until this grid has
+     * completed and flushed (step_kernel.cuh).  Hides launch latency between chained steps. */
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = step_smem_bytes<TJP, NS>();
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    NB_CUDA(cudaLaunchKernelEx(&cfg, step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>, p));
 }
 
 #define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR, FORM)                                        \
@@ -165,6 +178,7 @@ struct SimPipeline {
     int rank = 0, world = 1, local_gpus = 1, total_shards = 1;
     int exchange = nb::kExchangeNone;
     bool overlap = true;
+    bool pdl = true;          /* programmatic dependent launch between chained steps */
     int cur = 0;              /* which src_xy buffer holds the current positions */
     bool has_data = false;
     bool timed = false;       /* ev_begin/ev_end recorded at least once          */
@@ -268,6 +282,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
     NB_ASSERT(sim->local_gpus <= kMaxDst, "at most %d GPUs per process", kMaxDst);
     sim->total_shards = sim->world * sim->local_gpus;
     sim->overlap = !(cfg.flags & NB_SIM_FLAG_NO_OVERLAP) && !env_int("NBODY_NO_OVERLAP", 0);
+    sim->pdl = !env_int("NBODY_NO_PDL", 0);
 
     NB_CUDA(cudaSetDevice(first_dev));
     NB_CUDA(cudaGetDeviceProperties(&sim->prop, first_dev));
@@ -506,7 +521,7 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
 static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
     if (t1 <= t0) return;
     p.tile_first = t0;
-    sim->plan.var->launch((t1 - t0) * sim->plan.nslab, sh.stream, p);
+    sim->plan.var->launch((t1 - t0) * sim->plan.nslab, sh.stream, p, sim->pdl);
     NB_CUDA(cudaGetLastError());
     sim->kernels_launched++;
 }

@@ -48,6 +48,12 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
 
+    /* Programmatic dependent launch (no-ops when the launch did not ask for it): let the next step's
+     * grid be scheduled as soon as every CTA of this one has started, and do not touch global memory
+     * before the previous step's grid has completed and its writes are visible. */
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
     /* targets -> registers, negated.  Source-packed: one target duplicated into both halves of an
      * f32x2; target-packed: targets 2k and 2k+1 of this thread side by side. */
     float2 ntx[TR], nty[TR], rho[TR], ax[TR], ay[TR];

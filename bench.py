@@ -107,10 +107,22 @@ class ClockSampler:
 
 # ---- the reference's CPU path, timed on a bounded sample -----------------------------------------
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is entitled to all host threads."""
+    import ctypes as C
+    n = len(os.sched_getaffinity(0))
+    try:
+        C.CDLL("libgomp.so.1").omp_set_num_threads(n)
+    except OSError:
+        pass
+    return n
+
+
 def cpu_reference_runner():
     """Returns (kind, threads, step_range(arr, mass_len, first, last, dt)) for the CPU arm."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from _oracle import Oracle, RefLib
+    use_all_host_threads()
     if RefLib.available("avx"):
         r = RefLib("avx")
         return "reference", r.threads(), r.lib.refglue_step_range, "oracle/_ref/libnbody_ref.so (gcc -O3 -DUSE_AVX -mavx -fopenmp)"

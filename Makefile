@@ -14,8 +14,9 @@ CXX     := /usr/bin/g++
 
 ARCH    := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -ccbin $(CXX) -Xcompiler -fPIC -Xptxas -v -Iinclude -Inbody_b200/csrc
-# -mavx like the reference's default SIMD_SET=AVX; -ffp-contract=off keeps host float math FMA-free
-CFLAGS  := -O3 -std=gnu11 -fPIC -fopenmp -mavx -ffp-contract=off -fno-fast-math -Wall -Wextra -Iinclude
+# -mavx like the reference's default SIMD_SET=AVX; -ffp-contract=off keeps host float math FMA-free;
+# -fno-math-errno lets gcc vectorise sqrtf (vsqrtps) in UpdateWorld_CPU without changing any rounding
+CFLAGS  := -O3 -std=gnu11 -fPIC -fopenmp -mavx -ffp-contract=off -fno-fast-math -fno-math-errno -Wall -Wextra -Iinclude
 
 SRC     := nbody_b200/csrc
 OBJ     := build

@@ -37,7 +37,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--n", type=int, default=1 << 20, help="particles (default: N=1M, the metric's config)")
+    # "--particles" because torchrun's own parser rejects "--n" as an ambiguous abbreviation of its options
+    ap.add_argument("--n", "--particles", dest="n", type=int, default=1 << 20,
+                    help="particles (default: N=1M, the metric's config)")
     ap.add_argument("--galaxies", type=int, default=2)
     ap.add_argument("--seed", type=int, default=11037)
     ap.add_argument("--dt", type=float, default=1.0, help="ref src/bench.c:21 UPDATE_STEP")

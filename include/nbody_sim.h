@@ -144,6 +144,17 @@ int32_t NbSimDeviceCount(void);
  * softening), out[4] = sum m, out[5..6] = sum m x.  Synchronises. */
 void NbSimDiagnostics(SimPipeline *sim, double *out7);
 
+/* Headless stand-in for the reference GUI's DrawParticles / CreateCamera (ref src/main.c:198-250):
+ * a CUDA point splat of the current device state into a WIDTH x HEIGHT RGBA8 image (row-major, top row
+ * first, 4 bytes per pixel) copied to RGBA.  Every particle is a filled disc centred on its position
+ * truncated to an integer, radius max(radius, MIN_RADIUS) world units, colour by mass class, painted in
+ * array order (higher index wins); screen = (world - target) * zoom + (WIDTH/2, HEIGHT/2).
+ * NbSimFitCamera returns the camera that fits all particles into 90 % of the image (zoom <= 1), like the
+ * reference's CreateCamera.  Both synchronise; with several processes every rank must call them. */
+void NbSimFitCamera(SimPipeline *sim, int32_t width, int32_t height, float *target_x, float *target_y, float *zoom);
+void NbSimRenderRGBA(SimPipeline *sim, int32_t width, int32_t height, float target_x, float target_y, float zoom,
+                     float min_radius, uint8_t *rgba);
+
 /* FP64 accelerations of targets [first, last) from the current device state, written
  * as (ax, ay) doubles to OUT (2 * (last - first) values).  Does not advance the state. */
 void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out);

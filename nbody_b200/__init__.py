@@ -25,10 +25,11 @@ from .api import (  # noqa: F401
     lib,
     make_galaxies,
     plan,
+    write_ppm,
 )
 
 __all__ = [
     "PARTICLE", "PinnedParticles", "LIB_PATH", "CreateWorld", "DestroyWorld", "GetWorldParticles", "MakeGalaxies",
     "SimConfig", "SimPipeline", "UpdateWorld_CPU", "UpdateWorld_GPU", "World", "device_count",
-    "get_unique_id", "lib", "make_galaxies", "plan",
+    "get_unique_id", "lib", "make_galaxies", "plan", "write_ppm",
 ]

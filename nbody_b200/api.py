@@ -123,6 +123,8 @@ def lib():
         "NbSimPlan": (None, [u32, u32, C.c_int32, C.c_int32, C.POINTER(SimPlanInfo), vp]),
         "NbSimDiagnostics": (None, [vp, vp]),
         "NbSimAccF64": (None, [vp, u32, u32, vp]),
+        "NbSimFitCamera": (None, [vp, C.c_int32, C.c_int32, C.POINTER(f32), C.POINTER(f32), C.POINTER(f32)]),
+        "NbSimRenderRGBA": (None, [vp, C.c_int32, C.c_int32, f32, f32, f32, f32, vp]),
         # world.c extras
         "NbWorldPipeline": (vp, [vp]),
         "NbWorldMassLen": (u32, [vp]),
@@ -226,6 +228,14 @@ class PinnedParticles:
             self.close()
         except Exception:
             pass
+
+
+def write_ppm(path, rgba):
+    """Binary PPM (P6) of an RGBA image from SimPipeline.render -- the 'window' of a headless box."""
+    h, w = rgba.shape[:2]
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (w, h))
+        f.write(np.ascontiguousarray(rgba[:, :, :3]).tobytes())
 
 
 def get_unique_id():
@@ -335,6 +345,19 @@ class SimPipeline:
         out = np.zeros(7, dtype=np.float64)
         lib().NbSimDiagnostics(self._sim, out.ctypes.data_as(C.c_void_p))
         return dict(P=out[0:2].copy(), K=out[2], U=out[3], E=out[2] + out[3], M=out[4], C=out[5:7].copy())
+
+    def fit_camera(self, width, height):
+        """(target_x, target_y, zoom) fitting all particles into 90 % of the image (ref main.c:198-225)."""
+        tx, ty, zoom = C.c_float(), C.c_float(), C.c_float()
+        lib().NbSimFitCamera(self._sim, width, height, C.byref(tx), C.byref(ty), C.byref(zoom))
+        return tx.value, ty.value, zoom.value
+
+    def render(self, width, height, camera=None, min_radius=0.0):
+        """Headless DrawParticles (ref main.c:237-250): (height, width, 4) uint8 RGBA image."""
+        tx, ty, zoom = camera if camera is not None else self.fit_camera(width, height)
+        img = np.empty((height, width, 4), dtype=np.uint8)
+        lib().NbSimRenderRGBA(self._sim, width, height, tx, ty, zoom, min_radius, img.ctypes.data_as(C.c_void_p))
+        return img
 
     def acc_f64(self, first=0, last=None):
         last = self.total_len if last is None else last

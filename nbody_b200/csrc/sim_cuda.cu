@@ -18,6 +18,7 @@
 #include "layout_kernels.cuh"
 #include "nbody_sim.h"
 #include "nccl_dyn.h"
+#include "render_kernels.cuh"
 #include "step_kernel.cuh"
 #include "util.cuh"
 
@@ -717,10 +718,12 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     out->pairs_per_step = (uint64_t)sim->data.total_len * sim->data.mass_len;
 }
 
-void NbSimDiagnostics(SimPipeline *sim, double *out7) {
-    /* bring one full AoS copy up to date on the host side of the API, then reduce on GPU 0 */
+/* Bring the AoS copy on the first GPU up to date with the whole current state (collective when
+ * several processes share the World: every rank must call it). */
+static void refresh_aos_on_first_gpu(SimPipeline *sim) {
     const uint32_t N = sim->data.total_len;
     nb::Shard &sh = sim->shards[0];
+    NB_ASSERT(sim->has_data, "no particle data on the device yet");
     if (sim->total_shards > 1) {
         Particle *tmp = (Particle *)NbSimHostAlloc((size_t)N * sizeof(Particle));
         nb::download(sim, tmp);
@@ -732,12 +735,63 @@ void NbSimDiagnostics(SimPipeline *sim, double *out7) {
         NB_CUDA(cudaSetDevice(sh.device));
         nb::pack_own_ranges(sim, sh);
     }
+}
+
+void NbSimDiagnostics(SimPipeline *sim, double *out7) {
+    const uint32_t N = sim->data.total_len;
+    nb::Shard &sh = sim->shards[0];
+    refresh_aos_on_first_gpu(sim);
     NB_CUDA(cudaMemsetAsync(sh.scratch64, 0, 7 * sizeof(double), sh.stream));
     nb::diagnostics_kernel<<<nb::ceil_div(N, 256), 256, 0, sh.stream>>>(sh.aos, N, sim->data.mass_len, sh.scratch64);
     NB_CUDA(cudaGetLastError());
     sim->kernels_launched++;
     NB_CUDA(cudaMemcpyAsync(out7, sh.scratch64, 7 * sizeof(double), cudaMemcpyDeviceToHost, sh.stream));
     NB_CUDA(cudaStreamSynchronize(sh.stream));
+}
+
+void NbSimFitCamera(SimPipeline *sim, int32_t width, int32_t height, float *target_x, float *target_y, float *zoom) {
+    const uint32_t N = sim->data.total_len;
+    nb::Shard &sh = sim->shards[0];
+    refresh_aos_on_first_gpu(sim);
+    int *d = nb::dev_alloc<int>(4);
+    const int init[4] = {nb::float_to_ordered_host(INFINITY), nb::float_to_ordered_host(INFINITY),
+                         nb::float_to_ordered_host(-INFINITY), nb::float_to_ordered_host(-INFINITY)};
+    NB_CUDA(cudaMemcpyAsync(d, init, sizeof init, cudaMemcpyHostToDevice, sh.stream));
+    nb::bounds_kernel<<<nb::ceil_div(N, 256), 256, 0, sh.stream>>>(sh.aos, N, d);
+    NB_CUDA(cudaGetLastError());
+    sim->kernels_launched++;
+    int h[4];
+    NB_CUDA(cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, sh.stream));
+    NB_CUDA(cudaStreamSynchronize(sh.stream));
+    NB_CUDA(cudaFree(d));
+    const float minx = nb::ordered_to_float_host(h[0]), miny = nb::ordered_to_float_host(h[1]);
+    const float maxx = nb::ordered_to_float_host(h[2]), maxy = nb::ordered_to_float_host(h[3]);
+    /* ref src/main.c:212-222: fit 90 % of the window, never zoom in beyond 1 */
+    const float zx = 0.9f * (float)width / (maxx - minx), zy = 0.9f * (float)height / (maxy - miny);
+    *zoom = (zx < 1.f || zy < 1.f) ? fminf(zx, zy) : 1.f;
+    *target_x = (minx + maxx) * 0.5f;
+    *target_y = (miny + maxy) * 0.5f;
+}
+
+void NbSimRenderRGBA(SimPipeline *sim, int32_t width, int32_t height, float target_x, float target_y, float zoom,
+                     float min_radius, uint8_t *rgba) {
+    NB_ASSERT(width > 0 && height > 0 && (int64_t)width * height <= (1 << 28), "bad image size %d x %d", width, height);
+    const uint32_t N = sim->data.total_len;
+    const uint32_t pixels = (uint32_t)width * (uint32_t)height;
+    nb::Shard &sh = sim->shards[0];
+    refresh_aos_on_first_gpu(sim);
+    unsigned *winner = nb::dev_alloc<unsigned>(pixels);
+    uchar4 *img = nb::dev_alloc<uchar4>(pixels);
+    NB_CUDA(cudaMemsetAsync(winner, 0, (size_t)pixels * sizeof(unsigned), sh.stream));
+    const nb::Camera cam = {target_x, target_y, zoom, width, height};
+    nb::splat_kernel<<<nb::ceil_div(N, 8), 256, 0, sh.stream>>>(sh.aos, N, cam, min_radius, winner);
+    nb::resolve_kernel<<<nb::ceil_div(pixels, 256), 256, 0, sh.stream>>>(sh.aos, winner, pixels, img);
+    NB_CUDA(cudaGetLastError());
+    sim->kernels_launched += 2;
+    NB_CUDA(cudaMemcpyAsync(rgba, img, (size_t)pixels * 4, cudaMemcpyDeviceToHost, sh.stream));
+    NB_CUDA(cudaStreamSynchronize(sh.stream));
+    NB_CUDA(cudaFree(winner));
+    NB_CUDA(cudaFree(img));
 }
 
 void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out) {

@@ -5,10 +5,10 @@ OUT=gpurun_out; mkdir -p $OUT; PORT=29700
 run() { # gpus n tag
   PORT=$((PORT+1))
   if [ $1 -eq 1 ]; then
-    timeout 400 python bench.py --gpus 1 --n $2 --steps 3 --warmup 3 --no-cpu-baseline > $OUT/c5_$3.json 2> $OUT/c5_$3.err
+    timeout 400 python bench.py --gpus 1 --particles $2 --steps 3 --warmup 3 --no-cpu-baseline > $OUT/c5_$3.json 2> $OUT/c5_$3.err
   else
     timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $1 --master-addr 127.0.0.1 --master-port $PORT \
-      bench.py --gpus $1 --n $2 --steps 3 --warmup 3 --no-cpu-baseline > $OUT/c5_$3.json 2> $OUT/c5_$3.err
+      bench.py --gpus $1 --particles $2 --steps 3 --warmup 3 --no-cpu-baseline > $OUT/c5_$3.json 2> $OUT/c5_$3.err
   fi
   python - <<PY
 import json
@@ -19,6 +19,9 @@ except Exception as e:
     print("$3 failed", e)
 PY
 }
+if [ "${ONLY_MULTI:-0}" = "1" ]; then
+  run 8 4194304 strong4m_g8; run 2 2097152 weak_g2; run 4 2965821 weak_g4; exit 0
+fi
 run 8 4194304 strong4m_g8
 run 1 4194304 strong4m_g1
 run 1 1482910 weak_g1

@@ -162,21 +162,25 @@ static void cpu_snapshot(World *w) {
     }
 }
 
+typedef float Lanes __attribute__((vector_size(CPU_LANES * sizeof(float)), aligned(32)));
+
 static void cpu_update_one(Particle *p, const float *sx, const float *sy, const float *sgm, uint32_t padded,
                            float dt) {
-    float ax[CPU_LANES] = {0}, ay[CPU_LANES] = {0};
+    /* one 8-lane accumulator per axis, kept in registers (GCC vector extension; with -mavx these are
+     * single ymm operations, every one separately rounded: -ffp-contract=off) */
+    Lanes ax = {0}, ay = {0};
     const float x = p->pos.x, y = p->pos.y, soft = p->radius;
+    const Lanes x8 = {x, x, x, x, x, x, x, x}, y8 = {y, y, y, y, y, y, y, y};
+    const Lanes soft8 = {soft, soft, soft, soft, soft, soft, soft, soft};
     for (uint32_t base = 0; base < padded; base += CPU_LANES) {
-        #pragma omp simd
-        for (int s = 0; s < CPU_LANES; s++) {
-            const float dx = sx[base + s] - x;
-            const float dy = sy[base + s] - y;
-            const float r2 = (dx * dx + dy * dy) + soft;
-            const float r3 = sqrtf(r2) * r2;
-            const float f = sgm[base + s] / r3;
-            ax[s] += dx * f;
-            ay[s] += dy * f;
-        }
+        const Lanes dx = *(const Lanes *)(sx + base) - x8;
+        const Lanes dy = *(const Lanes *)(sy + base) - y8;
+        const Lanes r2 = (dx * dx + dy * dy) + soft8;
+        Lanes r1;
+        for (int s = 0; s < CPU_LANES; s++) r1[s] = sqrtf(r2[s]); /* vsqrtps under -fno-math-errno */
+        const Lanes f = *(const Lanes *)(sgm + base) / (r1 * r2);
+        ax += dx * f;
+        ay += dy * f;
     }
     float sum_x = 0.f, sum_y = 0.f;
     for (int s = CPU_LANES - 1; s >= 0; s--) sum_x += ax[s];

@@ -29,6 +29,7 @@ namespace nb {
 struct Variant {
     const char *name;
     int threads, T, tjp, ns, minb, unr;
+    double rel_cost; /* measured time per pair relative to the best variant at large N (0: not a plan candidate) */
     size_t smem;
     const void *func;
     void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl);
@@ -52,21 +53,23 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     NB_CUDA(cudaLaunchKernelEx(&cfg, step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>, p));
 }
 
-#define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR, FORM)                                        \
+#define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR, FORM, REL)                                   \
     {                                                                                                 \
-        NAME, THREADS, T, TJP, NS, MINB, UNR, step_smem_bytes<TJP, NS>(),                             \
+        NAME, THREADS, T, TJP, NS, MINB, UNR, REL, step_smem_bytes<TJP, NS>(),                        \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>                                      \
     }
 
 static const Variant kVariants[] = {
-    NB_VARIANT("t512x4", 512, 4, 128, 4, 1, 2, kFormPacked), /* default for large N: 2048 targets per CTA */
-    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2, kFormPacked), /* 1024 targets per CTA                       */
-    NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2, kFormPacked), /* 512 targets per CTA                        */
-    NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2, kFormPacked),  /* 256 targets per CTA, small N               */
-    NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked),
-    NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked),
-    NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2, kFormPacked),    /* 256 targets per CTA, 2 warps               */
+    /* plan candidates, with their measured cost per pair relative to t512x4 (profiles/r01_tune_sweep*.txt) */
+    NB_VARIANT("t512x4", 512, 4, 128, 4, 1, 2, kFormPacked, 1.000), /* 2048 targets per CTA, 1 CTA/SM  */
+    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2, kFormPacked, 1.010), /* 1024 targets per CTA            */
+    NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2, kFormPacked, 1.025), /* 512 targets per CTA             */
+    NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2, kFormPacked, 1.065),  /* 256 targets per CTA, small N    */
+    /* selectable with NBODY_VARIANT only */
+    NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked, 0.0),
+    NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked, 0.0),
+    NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2, kFormPacked, 0.0),
 };
 static const int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
@@ -87,22 +90,75 @@ struct Plan {
 static uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 
 /*
- * Slab choice.  One launch has tiles*nslab CTAs on slots = SMs * CTAs/SM; the modelled time is
- * waves * (pairs per CTA + fixed cost).  We minimise the sum over g in {1,2,4,8} GPUs (each g
- * weighting equally, tiles split g ways) because the slab length fixes the summation order and
- * must not depend on how many GPUs run the World (results are bit-identical across g).
+ * Work plan = (kernel variant, slab length), chosen together by a timing model fitted to sweeps on
+ * B200 (tools/tune.cu sweep; fit within ~3 % for N >= 50K, ~10 % below):
+ *
+ *   a grid of C = tiles * nslab CTAs runs as full waves of `slots` = SMs * CTAs/SM plus one partial
+ *   wave; a CTA computes tile * slab pairs; an SM delivers `kPairsPerClk` pairs per clock when 16 or
+ *   more warps are resident and a fraction 0.7 + 0.3 * warps/16 of that below; every wave pays a fixed
+ *   prologue/epilogue cost and every launch a fixed latency.
+ *
+ * The plan fixes the summation order (tile size, slab boundaries), so it must not depend on how many
+ * GPUs run the World: the model is evaluated for the World split over 1, 2, 4 and 8 GPUs and the
+ * weighted total GPU time is minimised (1 and 8 GPUs weigh most).  Results are bit-identical across
+ * GPU counts because of this.
  */
-static void choose_slabs(Plan &pl, uint32_t slots, uint32_t forced_slab_len) {
+static const double kPairsPerClk = 12.0;    /* per SM at full occupancy, best variant (65.5 % of FP32 peak) */
+static const double kWaveFixedClk = 8000.0; /* per wave of CTAs: first TMA round trip, partial store, ticket, reduce */
+static const double kLaunchClk = 12000.0;   /* per launch */
+static const uint32_t kMinTiles = 48;       /* a variant needs this many target tiles to be a candidate */
+
+static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uint32_t slab_sources, int sm_count) {
+    const double ctas = (double)tiles * nslab;
+    const double slots = (double)v.minb * sm_count;
+    const int warps = v.threads / 32;
+    const double cta_pairs = (double)v.threads * v.T * slab_sources * v.rel_cost;
+    auto occ_eff = [](int w) { return w >= 16 ? 1.0 : 0.7 + 0.3 * w / 16.0; };
+    const double full = std::floor(ctas / slots), rem = ctas - full * slots;
+    double t = kLaunchClk;
+    if (full > 0) t += full * (cta_pairs * v.minb / (kPairsPerClk * occ_eff(v.minb * warps)) + kWaveFixedClk);
+    if (rem > 0) {
+        const int k = (int)std::ceil(rem / sm_count);
+        t += cta_pairs * k / (kPairsPerClk * occ_eff(k * warps)) + kWaveFixedClk;
+    }
+    return t;
+}
+
+static void set_geometry(Plan &pl, const Variant *v, uint32_t N, uint32_t M) {
+    pl.var = v;
+    pl.ctas_per_sm = v->minb;
+    pl.tile = (uint32_t)v->threads * v->T;
+    pl.ntiles = ceil_div(N, pl.tile);
+    pl.mtiles = ceil_div(M, pl.tile);
+    pl.n_pad = pl.ntiles * pl.tile;
+    pl.src_packs = ceil_div(M, 4);
+    pl.src_packs_pad = std::max(1u, ceil_div(pl.src_packs, (uint32_t)v->tjp)) * v->tjp;
+}
+
+/* Best slab count for one variant; returns the weighted model time (GPU-clocks summed over GPUs). */
+static double choose_slabs(Plan &pl, int sm_count, uint32_t forced_slab_len) {
     const uint32_t unr = 4; /* slab granularity in packs: a multiple of every variant's unroll */
+    static const int kGpus[4] = {1, 2, 4, 8};
+    static const double kWeight[4] = {4.0, 1.0, 1.0, 2.0};
+    auto weighted = [&](uint32_t ns, uint32_t sp) {
+        double cost = 0.0, wsum = 0.0;
+        for (int q = 0; q < 4; q++) {
+            const uint32_t g = (uint32_t)kGpus[q];
+            if (g > 1 && pl.ntiles < 2 * g) break;
+            cost += kWeight[q] * g * model_clocks(*pl.var, ceil_div(pl.ntiles, g), ns, sp * 4, sm_count);
+            wsum += kWeight[q];
+        }
+        return cost / wsum;
+    };
     if (pl.src_packs == 0) {
         pl.slab_packs = unr;
         pl.nslab = 1;
-        return;
+        return weighted(1, unr);
     }
     if (forced_slab_len) {
         pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
         pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
-        return;
+        return weighted(pl.nslab, pl.slab_packs);
     }
     const uint32_t min_packs = 32; /* >= 128 sources per slab */
     const uint32_t max_nslab = std::max(1u, std::min(4096u, pl.src_packs / min_packs));
@@ -110,20 +166,8 @@ static void choose_slabs(Plan &pl, uint32_t slots, uint32_t forced_slab_len) {
     uint32_t best_n = 1;
     for (uint32_t n = 1; n <= max_nslab; n++) {
         const uint32_t sp = ceil_div(ceil_div(pl.src_packs, n), unr) * unr;
-        const uint32_t ns = ceil_div(pl.src_packs, sp);
-        if (ns != n) continue;
-        const double cta_cost = (double)sp * 4.0 + 64.0 + 2.0 * ns; /* in sources per target */
-        double cost = 0.0;
-        int terms = 0;
-        for (uint32_t g = 1; g <= 8; g *= 2) {
-            const uint32_t tiles = ceil_div(pl.ntiles, g);
-            if (g > 1 && pl.ntiles < 2 * g) break;
-            const double waves = std::ceil((double)tiles * ns / slots);
-            /* ideal = tiles * src_packs*4 / slots */
-            cost += waves * cta_cost * slots / ((double)tiles * pl.src_packs * 4.0);
-            terms++;
-        }
-        cost /= terms;
+        if (ceil_div(pl.src_packs, sp) != n) continue;
+        const double cost = weighted(n, sp);
         if (cost < best * 0.999) {
             best = cost;
             best_n = n;
@@ -131,22 +175,16 @@ static void choose_slabs(Plan &pl, uint32_t slots, uint32_t forced_slab_len) {
     }
     pl.slab_packs = ceil_div(ceil_div(pl.src_packs, best_n), unr) * unr;
     pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
+    return best;
 }
 
-static const Variant *pick_variant(uint32_t total_len, int sm_count) {
-    if (const char *e = getenv("NBODY_VARIANT")) {
-        for (int i = 0; i < kNumVariants; i++)
-            if (strcmp(e, kVariants[i].name) == 0) return &kVariants[i];
-        NB_FAIL("NBODY_VARIANT=%s is not a known kernel variant", e);
-    }
-    /* The biggest tile that still leaves every SM several tiles, also when the World is later
-     * split over 8 GPUs (tile size fixes the summation order, so it must not depend on the GPU count). */
-    if (total_len >= (uint32_t)sm_count * 2048u * 3u) return &kVariants[0];
-    if (total_len >= (uint32_t)sm_count * 1024u) return &kVariants[1];
-    if (total_len >= (uint32_t)sm_count * 256u) return &kVariants[2];
-    return &kVariants[3];
+static const Variant *forced_variant() {
+    const char *e = getenv("NBODY_VARIANT");
+    if (!e || !*e) return nullptr;
+    for (int i = 0; i < kNumVariants; i++)
+        if (strcmp(e, kVariants[i].name) == 0) return &kVariants[i];
+    NB_FAIL("NBODY_VARIANT=%s is not a known kernel variant", e);
 }
-
 
 /* ---- pipeline state ------------------------------------------------------------------ */
 
@@ -212,15 +250,31 @@ static Tp *dev_alloc(size_t count) {
 /* Geometry from sizes alone -- no device is touched, so the same plan can be computed (and
  * tested) on a machine without a GPU.  Occupancy is the variant's __launch_bounds__ promise. */
 static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl) {
-    pl.var = pick_variant(N, sm_count);
-    pl.ctas_per_sm = pl.var->minb;
-    pl.tile = (uint32_t)pl.var->threads * pl.var->T;
-    pl.ntiles = ceil_div(N, pl.tile);
-    pl.mtiles = ceil_div(M, pl.tile);
-    pl.n_pad = pl.ntiles * pl.tile;
-    pl.src_packs = ceil_div(M, 4);
-    pl.src_packs_pad = std::max(1u, ceil_div(pl.src_packs, (uint32_t)pl.var->tjp)) * pl.var->tjp;
-    choose_slabs(pl, (uint32_t)pl.ctas_per_sm * sm_count, forced_slab);
+    if (const Variant *v = forced_variant()) {
+        set_geometry(pl, v, N, M);
+        choose_slabs(pl, sm_count, forced_slab);
+        return;
+    }
+    double best = 1e300;
+    Plan best_plan{};
+    const Variant *smallest = nullptr;
+    for (int i = 0; i < kNumVariants; i++)
+        if (kVariants[i].rel_cost > 0.0) smallest = &kVariants[i]; /* candidates are listed big to small */
+    for (int i = 0; i < kNumVariants; i++) {
+        if (kVariants[i].rel_cost <= 0.0) continue;
+        Plan cand{};
+        set_geometry(cand, &kVariants[i], N, M);
+        /* The model is validated where there are many tiles; with few, big tiles the per-tile costs it
+         * does not see (target load, last-CTA reduction of nslab partials by `tiles` CTAs only) dominate
+         * -- measured: N = 16K with 8 tiles of 2048 is 25 % slower than with 64 tiles of 256. */
+        if (cand.ntiles < kMinTiles && &kVariants[i] != smallest) continue;
+        const double cost = choose_slabs(cand, sm_count, forced_slab);
+        if (cost < best * 0.995) { /* prefer the earlier (larger-tile) variant on near ties */
+            best = cost;
+            best_plan = cand;
+        }
+    }
+    pl = best_plan;
 }
 
 /* Which tiles shard q of S computes: an equal share of the tiles holding massive particles

@@ -151,3 +151,22 @@ def test_library_is_sm100a_only(nb):
 
 def test_device_count_without_gpu_is_zero_or_more(nb):
     assert nb.device_count() >= 0
+
+
+def test_empty_world_is_legal_on_the_host_side(nb):
+    """size == 0: the reference's CPU side handles it (ref sim_cpu.c:109-111); here every call is a no-op."""
+    w = nb.CreateWorld(np.zeros(0, dtype=PARTICLE), 0)
+    assert len(nb.GetWorldParticles(w)) == 0
+    nb.UpdateWorld_CPU(w, 0.01, 3)
+    nb.UpdateWorld_GPU(w, 0.01, 3)        # no particles: returns before any device is touched
+    assert len(nb.GetWorldParticles(w)) == 0
+    nb.DestroyWorld(w)
+
+
+def test_two_worlds_coexist(nb, golden):
+    """bench.c creates a CPU and a GPU World from the same array (ref src/bench.c:55-56)."""
+    g = golden("galaxy_1000_2.npz")
+    with nb.World(g["input"]) as a, nb.World(g["input"]) as b:
+        a.update_cpu(float(g["dt"]), 1)
+        assert a.particles().tobytes() == g["step1"].tobytes()
+        assert b.particles().tobytes() == g["world0"].tobytes()

@@ -116,7 +116,17 @@ __device__ __forceinline__ float rsqrt_mufu(float x) {
  *                    dispatch cycles instead of two (tools/tune.cu `pipes`)
  *   kFormScalar      everything scalar
  */
-enum { kFormPacked = 0, kFormTargetPacked = 1, kFormScalarAcc = 2, kFormScalar = 3 };
+enum {
+    kFormPacked = 0,
+    kFormTargetPacked = 1,
+    kFormScalarAcc = 2,
+    kFormScalar = 3,
+    /* ablations for tools/tune.cu ONLY (wrong results on purpose; they isolate one cost of the dispatch
+     * model of DESIGN.md section 5): */
+    kAblateMufu = 4,     /* inv = r2 instead of rsqrt(r2): removes the 2 MUFU dispatch cycles          */
+    kAblateAccRead = 5,  /* ax += f*f, ay += dy*dy: each accumulate reads 2 register pairs, not 3       */
+    kAblateBoth = 6
+};
 
 template <int FORM>
 __device__ __forceinline__ void interact_two(const float2 x, const float2 y, const float2 g, const float2 ntx,
@@ -140,12 +150,21 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
         float2 r2 = __ffma2_rn(dy, dy, rho);
         r2 = __ffma2_rn(dx, dx, r2);
         float2 inv;
-        inv.x = rsqrt_mufu(r2.x);
-        inv.y = rsqrt_mufu(r2.y);
+        if constexpr (FORM == kAblateMufu || FORM == kAblateBoth) {
+            inv = r2;
+        } else {
+            inv.x = rsqrt_mufu(r2.x);
+            inv.y = rsqrt_mufu(r2.y);
+        }
         const float2 inv2 = __fmul2_rn(inv, inv);
         const float2 gi = __fmul2_rn(g, inv);
         const float2 f = __fmul2_rn(inv2, gi);
-        if constexpr (FORM == kFormScalarAcc) {
+        if constexpr (FORM == kAblateAccRead || FORM == kAblateBoth) {
+            /* same instruction count and dependences on dx (through r2), dy and f, but each accumulate
+             * FFMA2 reads two distinct register pairs instead of three */
+            ax = __ffma2_rn(f, f, ax);
+            ay = __ffma2_rn(dy, dy, ay);
+        } else if constexpr (FORM == kFormScalarAcc) {
             ax.x = __fmaf_rn(dx.x, f.x, ax.x);
             ax.y = __fmaf_rn(dx.y, f.y, ax.y);
             ay.x = __fmaf_rn(dy.x, f.x, ay.x);

@@ -104,6 +104,32 @@ __global__ void __launch_bounds__(256) pipe_kernel(float *out, int iters, ClockR
                     a[k + 4].x = fmaf(bb[k + 4].x, cc[k].x, a[k + 4].x);
                     a[k + 4].y = fmaf(bb[k + 4].y, cc[k].y, a[k + 4].y);
                 }
+            } else if (MODE == 15) {
+                /* FFMA2 reading two register pairs and one scalar broadcast to both halves */
+#pragma unroll
+                for (int k = 0; k < 8; k++) a[k] = __ffma2_rn(bb[k], make_float2(cc[k].x, cc[k].x), a[k]);
+            } else if (MODE == 16) {
+                /* "transposed" pair arithmetic: an f32x2 is (x, y) of ONE pair; scalar r2 / f chain; one
+                 * FFMA2 (d, f broadcast, acc) accumulates both components.  8 pairs per round. */
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const float2 d = __fadd2_rn(a[k], b);                  /* (dx, dy)            */
+                    float r2 = fmaf(d.y, d.y, c.x);
+                    r2 = fmaf(d.x, d.x, r2);
+                    const float inv = rsqrt_mufu(r2);
+                    const float f = (inv * inv) * (c.y * inv);
+                    a[k] = __ffma2_rn(d, make_float2(f, f), a[k]);
+                }
+            } else if (MODE == 17) {
+                /* same without the MUFU */
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const float2 d = __fadd2_rn(a[k], b);
+                    float r2 = fmaf(d.y, d.y, c.x);
+                    r2 = fmaf(d.x, d.x, r2);
+                    const float f = (r2 * r2) * (c.y * r2);
+                    a[k] = __ffma2_rn(d, make_float2(f, f), a[k]);
+                }
             } else if (MODE == 9) {
                 /* 8 FFMA2 + 2 independent MUFU: does a MUFU issue cost the FMA pipe a cycle? */
 #pragma unroll
@@ -221,6 +247,9 @@ static void pipes(int sms) {
         run_pipe<12>("FFMA scalar, 3 distinct registers", 4 * 16.0, "fma", sms, c);
         run_pipe<13>("FFMA2 pairs sharing one operand", 4 * 16.0, "fma", sms, c);
         run_pipe<14>("same as scalar FFMA x4", 4 * 16.0, "fma", sms, c);
+        run_pipe<15>("FFMA2, 2 pairs + 1 scalar broadcast", 4 * 16.0, "fma", sms, c);
+        run_pipe<16>("transposed mix incl. MUFU (pairs)", 4 * 8.0, "pair", sms, c);
+        run_pipe<17>("transposed mix without MUFU (pairs)", 4 * 8.0, "pair", sms, c);
         run_pipe<9>("8 FFMA2 + 2 MUFU (fma lanes)", 4 * 16.0, "fma", sms, c);
         run_pipe<11>("8 FFMA2 + 4 MUFU (fma lanes)", 4 * 16.0, "fma", sms, c);
         run_pipe<10>("8 FFMA2 + 2 int ALU (fma lanes)", 4 * 16.0, "fma", sms, c);
@@ -347,7 +376,7 @@ static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
     const double waves = (double)grid / (occ * sms);
     printf("  %s t%dx%d tjp%d ns%d unr%d minb%d | regs %3d occ %d | nslab %4u grid %6u waves %7.2f | best %8.3f ms avg %8.3f | "
            "%7.1f Gpairs/s  %5.1f%% of FP32 peak (14 flop/pair)  %5.1f%% of 9-slot ceiling\n",
-           FORM == 0 ? "packed" : FORM == 1 ? "tgtpack" : FORM == 2 ? "sclacc" : "scalar", THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
+           FORM == 0 ? "packed" : FORM == 1 ? "tgtpack" : FORM == 2 ? "sclacc" : FORM == 3 ? "scalar" : FORM == 4 ? "ABL-mufu" : FORM == 5 ? "ABL-acc" : "ABL-both", THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
            100.0 * rate * 14.0 / g_peak_flops, 100.0 * rate / g_peak_pairs);
     fflush(stdout);
 }
@@ -369,6 +398,13 @@ static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
         list.push_back(base);
     }
     for (uint32_t ns : list) {
+        if (set && !strcmp(set, "ablate")) {
+            run_variant<512, 4, 128, 4, 1, 2, 0>(b, ns, sms);
+            run_variant<512, 4, 128, 4, 1, 2, 4>(b, ns, sms);
+            run_variant<512, 4, 128, 4, 1, 2, 5>(b, ns, sms);
+            run_variant<512, 4, 128, 4, 1, 2, 6>(b, ns, sms);
+            continue;
+        }
         if (small) {
             run_variant<128, 2, 64, 4, 6, 2>(b, ns, sms);
             run_variant<64, 4, 64, 4, 8, 2>(b, ns, sms);

@@ -45,7 +45,7 @@ nbody_b200/bin/nbody-bench: $(SRC)/bench_cli.c $(LIB)
 	@mkdir -p $(dir $@)
 	$(CC) $(CFLAGS) -o $@ $(SRC)/bench_cli.c -Lnbody_b200/lib -lnbody -Wl,-rpath,'$$ORIGIN/../lib' -lm
 
-oracle:
+oracle: $(LIB)
 	$(MAKE) -C oracle all
 	@if [ -d /root/reference/src/lib ]; then $(MAKE) -C oracle ref; fi
 

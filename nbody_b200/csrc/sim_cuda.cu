@@ -106,6 +106,9 @@ static uint32_t ceil_div(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 static const double kPairsPerClk = 12.0;    /* per SM at full occupancy, best variant (65.5 % of FP32 peak) */
 static const double kWaveFixedClk = 8000.0; /* per wave of CTAs: first TMA round trip, partial store, ticket, reduce */
 static const double kLaunchClk = 12000.0;   /* per launch */
+static const uint32_t kMinTargetsPerGpu = 32768; /* below this a GPU is latency-bound: not a split to plan for */
+static const uint32_t kMinSlabs = 16;       /* accuracy floor, see choose_slabs */
+static const uint32_t kMaxSlabSources = 16384;
 static const uint32_t kMinTiles = 48;       /* a variant needs this many target tiles to be a candidate */
 
 static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uint32_t slab_sources, int sm_count) {
@@ -136,7 +139,7 @@ static void set_geometry(Plan &pl, const Variant *v, uint32_t N, uint32_t M) {
 }
 
 /* Best slab count for one variant; returns the weighted model time (GPU-clocks summed over GPUs). */
-static double choose_slabs(Plan &pl, int sm_count, uint32_t forced_slab_len) {
+static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
     const uint32_t unr = 4; /* slab granularity in packs: a multiple of every variant's unroll */
     static const int kGpus[4] = {1, 2, 4, 8};
     static const double kWeight[4] = {4.0, 1.0, 1.0, 2.0};
@@ -144,7 +147,8 @@ static double choose_slabs(Plan &pl, int sm_count, uint32_t forced_slab_len) {
         double cost = 0.0, wsum = 0.0;
         for (int q = 0; q < 4; q++) {
             const uint32_t g = (uint32_t)kGpus[q];
-            if (g > 1 && pl.ntiles < 2 * g) break;
+            /* a split is only worth planning for when every GPU keeps a throughput-bound share */
+            if (g > 1 && (pl.ntiles < 2 * g || N / g < kMinTargetsPerGpu)) break;
             cost += kWeight[q] * g * model_clocks(*pl.var, ceil_div(pl.ntiles, g), ns, sp * 4, sm_count);
             wsum += kWeight[q];
         }
@@ -162,9 +166,15 @@ static double choose_slabs(Plan &pl, int sm_count, uint32_t forced_slab_len) {
     }
     const uint32_t min_packs = 32; /* >= 128 sources per slab */
     const uint32_t max_nslab = std::max(1u, std::min(4096u, pl.src_packs / min_packs));
+    /* Accuracy floor: a register accumulator chain sums slab_len/2 terms, the reference's AVX build
+     * M/8 (ref sim_cpu.c:165-189).  At least kMinSlabs slabs keeps our chains 4x shorter than the
+     * reference's, so the CUDA result stays closer to FP64 than the reference is whatever the model
+     * would prefer (measured at N = 50K: 6 slabs p99 1.5e-5 vs FP64, 45 slabs 2.2e-6, reference 1.9e-5);
+     * and no chain is longer than kMaxSlabSources/2 terms however large the World is. */
+    const uint32_t min_nslab = std::min(std::max(kMinSlabs, ceil_div(pl.src_packs * 4, kMaxSlabSources)), max_nslab);
     double best = 1e300;
-    uint32_t best_n = 1;
-    for (uint32_t n = 1; n <= max_nslab; n++) {
+    uint32_t best_n = min_nslab;
+    for (uint32_t n = min_nslab; n <= max_nslab; n++) {
         const uint32_t sp = ceil_div(ceil_div(pl.src_packs, n), unr) * unr;
         if (ceil_div(pl.src_packs, sp) != n) continue;
         const double cost = weighted(n, sp);
@@ -175,6 +185,7 @@ static double choose_slabs(Plan &pl, int sm_count, uint32_t forced_slab_len) {
     }
     pl.slab_packs = ceil_div(ceil_div(pl.src_packs, best_n), unr) * unr;
     pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
+    if (best >= 1e300) best = weighted(pl.nslab, pl.slab_packs); /* no count in range divides evenly */
     return best;
 }
 
@@ -252,7 +263,7 @@ static Tp *dev_alloc(size_t count) {
 static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl) {
     if (const Variant *v = forced_variant()) {
         set_geometry(pl, v, N, M);
-        choose_slabs(pl, sm_count, forced_slab);
+        choose_slabs(pl, N, sm_count, forced_slab);
         return;
     }
     double best = 1e300;
@@ -268,7 +279,7 @@ static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab
          * does not see (target load, last-CTA reduction of nslab partials by `tiles` CTAs only) dominate
          * -- measured: N = 16K with 8 tiles of 2048 is 25 % slower than with 64 tiles of 256. */
         if (cand.ntiles < kMinTiles && &kVariants[i] != smallest) continue;
-        const double cost = choose_slabs(cand, sm_count, forced_slab);
+        const double cost = choose_slabs(cand, N, sm_count, forced_slab);
         if (cost < best * 0.995) { /* prefer the earlier (larger-tile) variant on near ties */
             best = cost;
             best_plan = cand;
@@ -576,7 +587,14 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
 static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
     if (t1 <= t0) return;
     p.tile_first = t0;
-    sim->plan.var->launch((t1 - t0) * sim->plan.nslab, sh.stream, p, sim->pdl);
+    /* Programmatic dependent launch pays when the grid is tiny (latency-bound) or fills the GPU for at
+     * least a wave.  In between, the next step's CTAs are parked early in whatever slots are free and
+     * then all start at once on an unevenly loaded set of SMs (measured: N = 16K with 576 CTAs on 888
+     * slots, 52 -> 72 us per chained step). */
+    const uint32_t grid = (t1 - t0) * sim->plan.nslab;
+    const uint32_t sms = (uint32_t)sim->prop.multiProcessorCount;
+    const bool pdl = sim->pdl && (grid <= sms || grid >= sms * (uint32_t)sim->plan.ctas_per_sm);
+    sim->plan.var->launch(grid, sh.stream, p, pdl);
     NB_CUDA(cudaGetLastError());
     sim->kernels_launched++;
 }

@@ -170,3 +170,15 @@ def test_two_worlds_coexist(nb, golden):
         a.update_cpu(float(g["dt"]), 1)
         assert a.particles().tobytes() == g["step1"].tobytes()
         assert b.particles().tobytes() == g["world0"].tobytes()
+
+
+def test_c_program_against_the_world_api(nb, tmp_path):
+    """A plain C user of include/nbody.h: the reference unit test's seven cases (tests/c/test_world_partition.c)."""
+    exe = str(tmp_path / "test_world_partition")
+    lib_dir = os.path.dirname(nb.LIB_PATH)
+    subprocess.run(["/usr/bin/gcc", "-std=gnu11", "-O1", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "tests", "c", "test_world_partition.c"), "-o", exe,
+                    "-L", lib_dir, "-lnbody", f"-Wl,-rpath,{lib_dir}", "-lm"], check=True)
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.count(" ok") == 7

@@ -55,10 +55,11 @@ struct StepParams {
     float2 *vel;              /* [total_len]                                              */
     float2 *acc;              /* [total_len]                                              */
     const float *radius;      /* [total_len]                                              */
-    float2 *part;             /* [nslab][n_pad] slab partial sums (nslab > 1)             */
+    float2 *part;             /* [nslab][part_stride] slab partial sums (nslab > 1)       */
     unsigned *tile_cnt;       /* [tiles] arrival tickets, zero between steps              */
     uint32_t total_len, mass_len;
-    uint32_t n_pad;           /* total_len rounded up to the target tile                  */
+    uint32_t part_stride;     /* targets this GPU computes, in whole tiles                */
+    uint32_t part_first;      /* particle index that maps to partial slot 0 in this launch */
     uint32_t src_packs_pad;   /* source packs incl. padding, multiple of TJP              */
     uint32_t slab_packs;      /* packs per slab (multiple of the inner unroll)            */
     uint32_t nslab;

@@ -409,7 +409,8 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         sh.vel = dev_alloc<float2>(N);
         sh.acc = dev_alloc<float2>(N);
         sh.radius = dev_alloc<float>(N);
-        sh.part = dev_alloc<float2>(pl.nslab > 1 ? (size_t)pl.nslab * pl.n_pad : 1);
+        /* partial sums only for the tiles this GPU computes: [nslab][own tiles * tile] */
+        sh.part = dev_alloc<float2>(pl.nslab > 1 ? (size_t)pl.nslab * ((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile : 1);
         sh.tile_cnt = dev_alloc<unsigned>(pl.ntiles);
         sh.scratch64 = dev_alloc<double>(8);
         NB_CUDA(cudaMemset(sh.tile_cnt, 0, sizeof(unsigned) * pl.ntiles));
@@ -579,7 +580,8 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
     p->pos = sh.pos; p->vel = sh.vel; p->acc = sh.acc; p->radius = sh.radius;
     p->part = sh.part; p->tile_cnt = sh.tile_cnt;
     p->total_len = sim->data.total_len; p->mass_len = sim->data.mass_len;
-    p->n_pad = pl.n_pad; p->src_packs_pad = pl.src_packs_pad;
+    p->part_stride = ((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile;
+    p->src_packs_pad = pl.src_packs_pad;
     p->slab_packs = pl.slab_packs; p->nslab = pl.nslab;
     p->dt = dt;
 }
@@ -587,6 +589,8 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
 static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
     if (t1 <= t0) return;
     p.tile_first = t0;
+    /* partial slots are local: the massive tiles [a0, a1) come first, the massless tiles [b0, b1) follow */
+    p.part_first = (t0 >= sh.b0 && t0 >= sh.a1 ? sh.b0 - (sh.a1 - sh.a0) : sh.a0) * sim->plan.tile;
     /* Programmatic dependent launch pays when the grid is tiny (latency-bound) or fills the GPU for at
      * least a wave.  In between, the next step's CTAs are parked early in whatever slots are free and
      * then all start at once on an unevenly loaded set of SMs (measured: N = 16K with 576 CTAs on 888

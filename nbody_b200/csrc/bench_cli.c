@@ -10,10 +10,11 @@
  *   --n N[,N...]     sizes instead of the reference's list
  *   --steps K        timed steps per call (default 100);  --warmup W (default 10)
  *   --galaxies G     galaxies per world (default 2)
+ *   --ngpus G        shard each World over G GPUs of this box (sets NBODY_NGPUS, which the library reads)
  *   --fresh-seed     re-seed before every size (each size then equals a stand-alone run)
  *   --json           one JSON object per size instead of the table
  *
- * The number of GPUs comes from env NBODY_NGPUS (the World API has no parameter for it).
+ * The World API has no parameter for the GPU count, so --ngpus travels through env NBODY_NGPUS.
  * Pair count per step = total_len * mass_len (massless particles are targets, never sources).
  */
 #include <stdbool.h>
@@ -75,10 +76,11 @@ int main(int argc, char **argv) {
         else if (!strcmp(argv[a], "--steps") && a + 1 < argc) steps = (uint32_t)atoi(argv[++a]);
         else if (!strcmp(argv[a], "--warmup") && a + 1 < argc) warmup = (uint32_t)atoi(argv[++a]);
         else if (!strcmp(argv[a], "--galaxies") && a + 1 < argc) galaxies = (uint32_t)atoi(argv[++a]);
+        else if (!strcmp(argv[a], "--ngpus") && a + 1 < argc) setenv("NBODY_NGPUS", argv[++a], 1);
         else {
             fprintf(stderr,
                     "usage: nbody-bench [--cpu|--gpu] [--n N,N,...] [--steps K] [--warmup W] [--galaxies G] "
-                    "[--fresh-seed] [--json]\n");
+                    "[--ngpus G] [--fresh-seed] [--json]\n");
             return 2;
         }
     }

@@ -126,7 +126,8 @@ enum {
      * model of DESIGN.md section 5): */
     kAblateMufu = 4,     /* inv = r2 instead of rsqrt(r2): removes the 2 MUFU dispatch cycles          */
     kAblateAccRead = 5,  /* ax += f*f, ay += dy*dy: each accumulate reads 2 register pairs, not 3       */
-    kAblateBoth = 6
+    kAblateBoth = 6,
+    kAblateReduce = 7    /* every slab CTA integrates its own partial: no partial store, ticket, reduction */
 };
 
 template <int FORM>

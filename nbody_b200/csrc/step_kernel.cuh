@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         }
     }
 
-    if (p.nslab == 1) {
+    if (p.nslab == 1 || FORM == kAblateReduce) {
 #pragma unroll
         for (int k = 0; k < T; k++) {
             const uint32_t i = i0 + k * THREADS;

@@ -377,7 +377,7 @@ static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
     const double waves = (double)grid / (occ * sms);
     printf("  %s t%dx%d tjp%d ns%d unr%d minb%d | regs %3d occ %d | nslab %4u grid %6u waves %7.2f | best %8.3f ms avg %8.3f | "
            "%7.1f Gpairs/s  %5.1f%% of FP32 peak (14 flop/pair)  %5.1f%% of 9-slot ceiling\n",
-           FORM == 0 ? "packed" : FORM == 1 ? "tgtpack" : FORM == 2 ? "sclacc" : FORM == 3 ? "scalar" : FORM == 4 ? "ABL-mufu" : FORM == 5 ? "ABL-acc" : "ABL-both", THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
+           FORM == 0 ? "packed" : FORM == 1 ? "tgtpack" : FORM == 2 ? "sclacc" : FORM == 3 ? "scalar" : FORM == 4 ? "ABL-mufu" : FORM == 5 ? "ABL-acc" : FORM == 6 ? "ABL-both" : "ABL-reduce", THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, grid, waves, best, sum / reps, rate * 1e-9,
            100.0 * rate * 14.0 / g_peak_flops, 100.0 * rate / g_peak_pairs);
     fflush(stdout);
 }
@@ -404,6 +404,13 @@ static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
             run_variant<512, 4, 128, 4, 1, 2, 4>(b, ns, sms);
             run_variant<512, 4, 128, 4, 1, 2, 5>(b, ns, sms);
             run_variant<512, 4, 128, 4, 1, 2, 6>(b, ns, sms);
+            continue;
+        }
+        if (set && !strcmp(set, "ablate-reduce")) {
+            run_variant<128, 2, 64, 4, 6, 2, 0>(b, ns, sms);
+            run_variant<128, 2, 64, 4, 6, 2, 7>(b, ns, sms);
+            run_variant<256, 4, 128, 4, 2, 2, 0>(b, ns, sms);
+            run_variant<256, 4, 128, 4, 2, 2, 7>(b, ns, sms);
             continue;
         }
         if (small) {

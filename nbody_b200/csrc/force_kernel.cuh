@@ -55,11 +55,11 @@ struct StepParams {
     float2 *vel;              /* [total_len]                                              */
     float2 *acc;              /* [total_len]                                              */
     const float *radius;      /* [total_len]                                              */
-    float2 *part;             /* [nslab][part_stride] slab partial sums (nslab > 1)       */
+    float2 *part;             /* slab partial sums (nslab > 1): part[slab * part_stride + i] for particle i.  The host */
+                              /* biases the pointer so that the first particle of the launch lands in slot 0      */
     unsigned *tile_cnt;       /* [tiles] arrival tickets, zero between steps              */
     uint32_t total_len, mass_len;
     uint32_t part_stride;     /* targets this GPU computes, in whole tiles                */
-    uint32_t part_first;      /* particle index that maps to partial slot 0 in this launch */
     uint32_t src_packs_pad;   /* source packs incl. padding, multiple of TJP              */
     uint32_t slab_packs;      /* packs per slab (multiple of the inner unroll)            */
     uint32_t nslab;

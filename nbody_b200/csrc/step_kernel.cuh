@@ -154,7 +154,7 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
 #pragma unroll
     for (int k = 0; k < T; k++) {
         const uint32_t i = i0 + k * THREADS;
-        __stcg(&p.part[(size_t)slab * p.part_stride + (i - p.part_first)], a[k]);
+        __stcg(&p.part[(size_t)slab * p.part_stride + i], a[k]);
     }
     __threadfence();
     __syncthreads();
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
             float2 v[8];
 #pragma unroll
             for (int u = 0; u < 8; u++)
-                if (s0 + u < p.nslab) v[u] = __ldcg(&p.part[(size_t)(s0 + u) * p.part_stride + (i - p.part_first)]);
+                if (s0 + u < p.nslab) v[u] = __ldcg(&p.part[(size_t)(s0 + u) * p.part_stride + i]);
 #pragma unroll
             for (int u = 0; u < 8; u++) {
                 if (s0 + u < p.nslab) {

@@ -349,7 +349,6 @@ static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
     p.part = b.part; p.tile_cnt = b.cnt;
     p.total_len = b.N; p.mass_len = b.M;
     p.part_stride = ntiles * tile;
-    p.part_first = 0;
     p.src_packs_pad = (b.src_packs + TJP - 1) / TJP * TJP;
     p.slab_packs = slab_packs; p.nslab = nslab;
     p.tile_first = 0;

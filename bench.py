@@ -250,7 +250,8 @@ def run_ours(args):
 
     def one_step():
         flush.zero_()                      # evict L2 between timed steps (untimed)
-        torch.cuda.synchronize()
+        barrier()                          # ranks start the step together: without it the skew of the untimed
+                                           # flush is counted as time spent waiting in the position exchange
         sim.step_async(1, args.dt)
         return sim.last_step_ms()          # CUDA events on the launching stream; synchronises
 

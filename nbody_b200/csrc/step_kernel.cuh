@@ -48,11 +48,31 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
 
-    /* Programmatic dependent launch (no-ops when the launch did not ask for it): let the next step's
-     * grid be scheduled as soon as every CTA of this one has started, and do not touch global memory
-     * before the previous step's grid has completed and its writes are visible. */
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    /* Programmatic dependent launch (no-op when the launch did not ask for it): this CTA may have been
+     * scheduled while the previous step was still draining; do not touch global memory before that grid
+     * has completed and its writes are visible. */
     asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    /* this CTA's slab, in packs */
+    const uint32_t pk0 = slab * p.slab_packs;
+    const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
+    const uint32_t npk = pk1 > pk0 ? pk1 - pk0 : 0;
+    const uint32_t ntile = (npk + TJP - 1) / TJP;
+
+    auto issue = [&](uint32_t k) { /* thread 0 only: fetch source tile k into stage k % NS */
+        const uint32_t s = k % NS;
+        const uint32_t f = k / NS;
+        if (f > 0) mbar_wait(&empty[s], (f - 1) & 1);
+        const uint32_t first = pk0 + k * TJP;
+        const uint32_t cnt = min((uint32_t)TJP, pk1 - first);
+        mbar_expect_tx(&full[s], cnt * 48u);
+        bulk_g2s(st_xy + (size_t)s * TJP * 2, p.src_xy + (size_t)first * 2, cnt * 32u, &full[s]);
+        bulk_g2s(st_gm + (size_t)s * TJP, p.src_gm + first, cnt * 16u, &full[s]);
+    };
+
+    if (tid == 0) {
+        for (uint32_t k = 0; k < (uint32_t)PF && k < ntile; k++) issue(k);
+    }
 
     /* targets -> registers, negated.  Source-packed: one target duplicated into both halves of an
      * f32x2; target-packed: targets 2k and 2k+1 of this thread side by side. */
@@ -83,28 +103,7 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         ax[k] = make_float2(0.f, 0.f);
         ay[k] = make_float2(0.f, 0.f);
     }
-    __syncthreads();
-
-    /* this CTA's slab, in packs */
-    const uint32_t pk0 = slab * p.slab_packs;
-    const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
-    const uint32_t npk = pk1 > pk0 ? pk1 - pk0 : 0;
-    const uint32_t ntile = (npk + TJP - 1) / TJP;
-
-    auto issue = [&](uint32_t k) { /* thread 0 only: fetch source tile k into stage k % NS */
-        const uint32_t s = k % NS;
-        const uint32_t f = k / NS;
-        if (f > 0) mbar_wait(&empty[s], (f - 1) & 1);
-        const uint32_t first = pk0 + k * TJP;
-        const uint32_t cnt = min((uint32_t)TJP, pk1 - first);
-        mbar_expect_tx(&full[s], cnt * 48u);
-        bulk_g2s(st_xy + (size_t)s * TJP * 2, p.src_xy + (size_t)first * 2, cnt * 32u, &full[s]);
-        bulk_g2s(st_gm + (size_t)s * TJP, p.src_gm + first, cnt * 16u, &full[s]);
-    };
-
-    if (tid == 0) {
-        for (uint32_t k = 0; k < (uint32_t)PF && k < ntile; k++) issue(k);
-    }
+    __syncthreads(); /* barrier inits visible to every thread before the first wait */
 
     for (uint32_t k = 0; k < ntile; k++) {
         if (tid == 0 && k + PF < ntile) issue(k + PF);
@@ -128,6 +127,9 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
     }
+
+    /* pair loop done: let the next step's grid be scheduled into the slots that free up from here on */
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     /* slab partial of each target.  Source-packed: even-source half + odd-source half;
      * target-packed: the two halves are two targets. */
@@ -168,31 +170,37 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
     if (!s_last) return;
     __threadfence();
 
-    /* last CTA of this target tile: add the slab partials in slab order and integrate */
+    /* last CTA of this target tile: add the slab partials in slab order and integrate.  The loads of
+     * 8 slabs of all T targets are in flight together (one L2 round trip per 8 slabs, not per target). */
+    float2 sum[T];
+    for (uint32_t s0 = 0; s0 < p.nslab; s0 += 8) {
+        float2 v[T][8];
 #pragma unroll
-    for (int k = 0; k < T; k++) {
-        const uint32_t i = i0 + k * THREADS;
-        if (i >= p.total_len) continue;
-        /* loads of 8 slabs in flight at a time (L2 latency), added strictly in slab order */
-        float2 sum = make_float2(0.f, 0.f);
-        for (uint32_t s0 = 0; s0 < p.nslab; s0 += 8) {
-            float2 v[8];
+        for (int k = 0; k < T; k++) {
+            const uint32_t i = i0 + k * THREADS;
 #pragma unroll
             for (int u = 0; u < 8; u++)
-                if (s0 + u < p.nslab) v[u] = __ldcg(&p.part[(size_t)(s0 + u) * p.part_stride + i]);
+                if (s0 + u < p.nslab) v[k][u] = __ldcg(&p.part[(size_t)(s0 + u) * p.part_stride + i]);
+        }
+#pragma unroll
+        for (int k = 0; k < T; k++) {
 #pragma unroll
             for (int u = 0; u < 8; u++) {
                 if (s0 + u < p.nslab) {
                     if (s0 + u == 0) {
-                        sum = v[0];
+                        sum[k] = v[k][0];
                     } else {
-                        sum.x = __fadd_rn(sum.x, v[u].x);
-                        sum.y = __fadd_rn(sum.y, v[u].y);
+                        sum[k].x = __fadd_rn(sum[k].x, v[k][u].x);
+                        sum[k].y = __fadd_rn(sum[k].y, v[k][u].y);
                     }
                 }
             }
         }
-        integrate_store(p, i, sum);
+    }
+#pragma unroll
+    for (int k = 0; k < T; k++) {
+        const uint32_t i = i0 + k * THREADS;
+        if (i < p.total_len) integrate_store(p, i, sum[k]);
     }
 }
 

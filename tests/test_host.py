@@ -149,6 +149,28 @@ def test_library_is_sm100a_only(nb):
     assert archs == {"sm_100a"}, archs
 
 
+def test_pair_loop_schedule_is_the_measured_one(nb):
+    """The order ptxas gives the pair loop is worth a few per cent, so the opcode sequence of
+    the built kernels must be the one the committed measurements were taken with (tools/sass_fingerprint.py)."""
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location(
+        "sass_fingerprint", os.path.join(os.path.dirname(__file__), "..", "tools", "sass_fingerprint.py"))
+    fpmod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fpmod)
+    if fpmod.cuobjdump() is None:
+        pytest.skip("cuobjdump unavailable")
+    want = json.load(open(fpmod.FINGERPRINT))
+    got = fpmod.fingerprint(nb.LIB_PATH)
+    for name, w in want.items():
+        g = got[name]
+        # per 32 pairs (two packs of 4 sources x 4 targets): 9 packed FP32 instructions and 2 MUFU per 2 pairs
+        assert g["loop_f32x2"] == w["loop_f32x2"] and g["loop_mufu"] == w["loop_mufu"], (name, g)
+        assert g["loop_sha1"] == w["loop_sha1"], (
+            f"{name}: ptxas scheduled the pair loop differently; re-measure on a B200, then "
+            "python tools/sass_fingerprint.py --update")
+
+
 def test_device_count_without_gpu_is_zero_or_more(nb):
     assert nb.device_count() >= 0
 

@@ -172,8 +172,10 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
             ay.x = __fmaf_rn(dy.x, f.x, ay.x);
             ay.y = __fmaf_rn(dy.y, f.y, ay.y);
         } else {
-            ax = __ffma2_rn(dx, f, ax);
-            ay = __ffma2_rn(dy, f, ay);
+            /* operand order and the loop structure of interact_pack are the ones of the best of 46 distinct
+             * ptxas schedules measured at N = 1M (profiles/r01_schedule_lottery.txt: 156.3 .. 160.7 ms) */
+            ax = __ffma2_rn(f, dx, ax);
+            ay = __ffma2_rn(f, dy, ay);
         }
     }
 }
@@ -186,11 +188,11 @@ __device__ __forceinline__ void interact_pack(const float4 xs, const float4 ys, 
     const float2 x01 = make_float2(xs.x, xs.y), x23 = make_float2(xs.z, xs.w);
     const float2 y01 = make_float2(ys.x, ys.y), y23 = make_float2(ys.z, ys.w);
     const float2 g01 = make_float2(gs.x, gs.y), g23 = make_float2(gs.z, gs.w);
+    /* sources 0,1 against every target, then sources 2,3: per target the same order as before */
 #pragma unroll
-    for (int t = 0; t < T; t++) {
-        interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
-        interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
-    }
+    for (int t = 0; t < T; t++) interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+#pragma unroll
+    for (int t = 0; t < T; t++) interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
 }
 
 /*

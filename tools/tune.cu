@@ -398,6 +398,11 @@ static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
         list.push_back(base);
     }
     for (uint32_t ns : list) {
+        if (set && !strcmp(set, "ship")) { /* the large-N kernel only */
+            run_variant<512, 4, 128, 4, 1, 2, 0>(b, ns, sms);
+            continue;
+        }
+#ifndef TUNE_MINIMAL
         if (set && !strcmp(set, "ablate")) {
             run_variant<512, 4, 128, 4, 1, 2, 0>(b, ns, sms);
             run_variant<512, 4, 128, 4, 1, 2, 4>(b, ns, sms);
@@ -448,6 +453,7 @@ static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
         run_variant<128, 8, 128, 4, 2, 1>(b, ns, sms);
         run_variant<64, 4, 64, 4, 8, 2>(b, ns, sms);
         run_variant<256, 3, 128, 4, 2, 2>(b, ns, sms);
+#endif
     }
 }
 
@@ -464,8 +470,11 @@ int main(int argc, char **argv) {
     printf("device %s, %d SMs, max SM clock %d MHz, FP32 peak %.2f TFLOP/s, 9-slot ceiling %.1f Gpairs/s\n", prop.name, sms,
            khz / 1000, g_peak_flops * 1e-12, g_peak_pairs * 1e-9);
     const char *cmd = argc > 1 ? argv[1] : "pipes";
+#ifndef TUNE_MINIMAL
     if (!strcmp(cmd, "pipes")) pipes(sms);
-    else if (!strcmp(cmd, "sweep")) {
+    else
+#endif
+    if (!strcmp(cmd, "sweep")) {
         const uint32_t N = argc > 2 ? (uint32_t)atol(argv[2]) : 262144;
         const uint32_t M = argc > 3 ? (uint32_t)atol(argv[3]) : N / 2;
         sweep(N, M, sms, argc > 4 ? argv[4] : nullptr);

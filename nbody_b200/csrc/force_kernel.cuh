@@ -39,6 +39,29 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+/* Source-order knobs of the pair arithmetic.  Every setting computes bit-identical results; they only change the
+ * order in which ptxas sees the operations, and with it the schedule of the pair loop, which is worth up to 2.8 %
+ * (tools/schedule_lottery.py builds all 144 settings, 46 distinct schedules; profiles/r01_schedule_lottery.txt:
+ * 156.3 .. 160.7 ms at N = 1M).  The defaults are the measured best. */
+#ifndef NB_ORD_ACC
+#define NB_ORD_ACC 1  /* 0: fma(dx, f, ax); fma(dy, f, ay)   1: fma(f, dx, ax); fma(f, dy, ay)   2: ay before ax */
+#endif
+#ifndef NB_ORD_R2
+#define NB_ORD_R2 0   /* 0: r2 = dx*dx + (dy*dy + rho)   1: r2 = dy*dy + (dx*dx + rho) -- NOT bit-identical to 0  */
+#endif
+#ifndef NB_ORD_GI
+#define NB_ORD_GI 0   /* 0: g * inv   1: inv * g */
+#endif
+#ifndef NB_ORD_F
+#define NB_ORD_F 0    /* 0: inv2 * gi   1: gi * inv2 */
+#endif
+#ifndef NB_ORD_SUB
+#define NB_ORD_SUB 0  /* 0: dx, dy   1: dy, dx   2: operands swapped */
+#endif
+#ifndef NB_ORD_LOOP
+#define NB_ORD_LOOP 1 /* 0: per target {sources 0,1; sources 2,3}   1: sources 0,1 for all targets, then 2,3 */
+#endif
+
 namespace nb {
 
 constexpr int kPack = 4;            /* sources per pack                                  */
@@ -147,10 +170,23 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
         ay.x = __fmaf_rn(dy0, f0, ay.x);
         ay.y = __fmaf_rn(dy1, f1, ay.y);
     } else {
+#if NB_ORD_SUB == 1
+        const float2 dy = __fadd2_rn(y, nty);
+        const float2 dx = __fadd2_rn(x, ntx);
+#elif NB_ORD_SUB == 2
+        const float2 dx = __fadd2_rn(ntx, x);
+        const float2 dy = __fadd2_rn(nty, y);
+#else
         const float2 dx = __fadd2_rn(x, ntx);
         const float2 dy = __fadd2_rn(y, nty);
+#endif
+#if NB_ORD_R2 == 1
+        float2 r2 = __ffma2_rn(dx, dx, rho);
+        r2 = __ffma2_rn(dy, dy, r2);
+#else
         float2 r2 = __ffma2_rn(dy, dy, rho);
         r2 = __ffma2_rn(dx, dx, r2);
+#endif
         float2 inv;
         if constexpr (FORM == kAblateMufu || FORM == kAblateBoth) {
             inv = r2;
@@ -159,8 +195,16 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
             inv.y = rsqrt_mufu(r2.y);
         }
         const float2 inv2 = __fmul2_rn(inv, inv);
+#if NB_ORD_GI == 1
+        const float2 gi = __fmul2_rn(inv, g);
+#else
         const float2 gi = __fmul2_rn(g, inv);
+#endif
+#if NB_ORD_F == 1
+        const float2 f = __fmul2_rn(gi, inv2);
+#else
         const float2 f = __fmul2_rn(inv2, gi);
+#endif
         if constexpr (FORM == kAblateAccRead || FORM == kAblateBoth) {
             /* same instruction count and dependences on dx (through r2), dy and f, but each accumulate
              * FFMA2 reads two distinct register pairs instead of three */
@@ -172,10 +216,16 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
             ay.x = __fmaf_rn(dy.x, f.x, ay.x);
             ay.y = __fmaf_rn(dy.y, f.y, ay.y);
         } else {
-            /* operand order and the loop structure of interact_pack are the ones of the best of 46 distinct
-             * ptxas schedules measured at N = 1M (profiles/r01_schedule_lottery.txt: 156.3 .. 160.7 ms) */
+#if NB_ORD_ACC == 1
             ax = __ffma2_rn(f, dx, ax);
             ay = __ffma2_rn(f, dy, ay);
+#elif NB_ORD_ACC == 2
+            ay = __ffma2_rn(dy, f, ay);
+            ax = __ffma2_rn(dx, f, ax);
+#else
+            ax = __ffma2_rn(dx, f, ax);
+            ay = __ffma2_rn(dy, f, ay);
+#endif
         }
     }
 }
@@ -188,11 +238,19 @@ __device__ __forceinline__ void interact_pack(const float4 xs, const float4 ys, 
     const float2 x01 = make_float2(xs.x, xs.y), x23 = make_float2(xs.z, xs.w);
     const float2 y01 = make_float2(ys.x, ys.y), y23 = make_float2(ys.z, ys.w);
     const float2 g01 = make_float2(gs.x, gs.y), g23 = make_float2(gs.z, gs.w);
-    /* sources 0,1 against every target, then sources 2,3: per target the same order as before */
+#if NB_ORD_LOOP == 1
+    /* sources 0,1 against every target, then sources 2,3: per target the same order either way */
 #pragma unroll
     for (int t = 0; t < T; t++) interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
 #pragma unroll
     for (int t = 0; t < T; t++) interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+#else
+#pragma unroll
+    for (int t = 0; t < T; t++) {
+        interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+        interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+    }
+#endif
 }
 
 /*

@@ -403,6 +403,18 @@ static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
             continue;
         }
 #ifndef TUNE_MINIMAL
+        if (set && !strcmp(set, "warps")) { /* 16 .. 24 resident warps per SM at 4 targets per thread */
+            run_variant<512, 4, 128, 4, 1, 2>(b, ns, sms);
+            run_variant<576, 4, 128, 4, 1, 2>(b, ns, sms);
+            run_variant<192, 4, 128, 4, 3, 2>(b, ns, sms);
+            run_variant<640, 4, 128, 4, 1, 2>(b, ns, sms);
+            run_variant<640, 4, 128, 4, 1, 1>(b, ns, sms);
+            run_variant<128, 4, 128, 4, 5, 2>(b, ns, sms);
+            run_variant<128, 4, 128, 4, 5, 1>(b, ns, sms);
+            run_variant<320, 4, 128, 4, 2, 1>(b, ns, sms);
+            run_variant<768, 4, 128, 4, 1, 1>(b, ns, sms);
+            continue;
+        }
         if (set && !strcmp(set, "ablate")) {
             run_variant<512, 4, 128, 4, 1, 2, 0>(b, ns, sms);
             run_variant<512, 4, 128, 4, 1, 2, 4>(b, ns, sms);

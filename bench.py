@@ -294,9 +294,10 @@ def run_ours(args):
             host[:] = arr
 
             def e2e_step():
-                sim.set_data(host)                 # sim_gpu.h seam: H2D
+                sim.set_data(host)                 # sim_gpu.h seam: H2D of the particles this rank owns,
+                                                   # source data replicated GPU to GPU (NCCL)
                 sim.update(1, args.dt)
-                sim.get_data(host)                 # D2H (+ gather of the other ranks' slices)
+                sim.get_data_local(host)           # D2H of the particles this rank owns (sharded read-back)
         e2e_step()
         barrier()
         t0 = time.perf_counter()
@@ -312,7 +313,7 @@ def run_ours(args):
                "h2d_bytes_per_step": int(len(arr)) * 32, "d2h_bytes_per_step": int(len(arr)) * 32,
                "ms_per_step": dt_e2e / n_e2e * 1e3, "steps": n_e2e,
                "api": "CreateWorld/UpdateWorld_GPU/GetWorldParticles" if world == 1
-                      else "SetSimulationData/PerformSimUpdate/GetSimulationData per rank"}
+                      else "SetSimulationData/PerformSimUpdate/NbSimGetDataLocal per rank (each rank moves its own shard)"}
         if world == 1:
             wld.close()
 

@@ -50,7 +50,9 @@ void DestroySimPipeline(SimPipeline *sim);
 /* Device -> PS: total_len Particles in World order.  (ref sim_gpu.h:27) */
 void GetSimulationData(const SimPipeline *sim, Particle *ps);
 
-/* PS -> device: total_len Particles in World order (massive first).  (ref sim_gpu.h:30) */
+/* PS -> device: total_len Particles in World order (massive first).  (ref sim_gpu.h:30)
+ * With several GPUs (NBODY_NGPUS, or one process per GPU) every GPU copies only the particles it
+ * owns out of PS and the source data is replicated GPU to GPU; every rank passes the same array. */
 void SetSimulationData(SimPipeline *sim, const Particle *ps);
 
 /* N > 0 chained steps of size DT; returns after the device finished.  Data MUST have
@@ -93,6 +95,13 @@ void NbSimSynchronize(SimPipeline *sim);
 /* Device-side time of the most recent NbSimStepAsync/PerformSimUpdate call in ms (CUDA
  * events on the launching stream, max over this process' GPUs); synchronises. */
 float NbSimLastStepMs(SimPipeline *sim);
+
+/* One process per GPU: like GetSimulationData, but only the particles owned by THIS process' GPUs are
+ * written to PS (same indices as in the full array; the rest of PS is left alone) and nothing is gathered
+ * from the other ranks -- the sharded read-back of a sharded World.  NbSimLocalRanges returns those index
+ * ranges: up to 2 per GPU of this process, OUT[2k], OUT[2k+1] = [first, last); returns the number of ranges. */
+void NbSimGetDataLocal(SimPipeline *sim, Particle *ps);
+uint32_t NbSimLocalRanges(const SimPipeline *sim, uint32_t *out, uint32_t max_ranges);
 
 /* Page-locked host memory for Particle arrays, so uploads/downloads run at link speed. */
 void *NbSimHostAlloc(size_t bytes);

@@ -118,6 +118,8 @@ def lib():
         "NbSimLastStepMs": (f32, [vp]),
         "NbSimHostAlloc": (vp, [C.c_size_t]),
         "NbSimHostFree": (None, [vp]),
+        "NbSimGetDataLocal": (None, [vp, vp]),
+        "NbSimLocalRanges": (C.c_uint32, [vp, vp, C.c_uint32]),
         "NbSimGetInfo": (None, [vp, C.POINTER(SimInfo)]),
         "NbSimDeviceCount": (C.c_int32, []),
         "NbSimPlan": (None, [u32, u32, C.c_int32, C.c_int32, C.POINTER(SimPlanInfo), vp]),
@@ -323,6 +325,18 @@ class SimPipeline:
             out = np.empty(self.total_len, dtype=PARTICLE)
         lib().GetSimulationData(self._sim, out.ctypes.data_as(C.c_void_p))
         return out
+
+    def get_data_local(self, out):
+        """Sharded read-back: only the particles owned by this process' GPUs are written to OUT (full-size array)."""
+        assert len(out) == self.total_len and out.dtype == PARTICLE
+        lib().NbSimGetDataLocal(self._sim, out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def local_ranges(self):
+        """[(first, last), ...] particle index ranges owned by this process' GPUs."""
+        buf = (C.c_uint32 * 64)()
+        n = lib().NbSimLocalRanges(self._sim, buf, 32)
+        return [(int(buf[2 * k]), int(buf[2 * k + 1])) for k in range(min(n, 32))]
 
     def update(self, n, dt):
         lib().PerformSimUpdate(self._sim, n, dt)

@@ -34,11 +34,12 @@ __global__ void unpack_targets_kernel(const Particle *__restrict__ aos, uint32_t
  * (the reference multiplies per pair, ref sim_cpu.c:179 -- same single rounding).  Slots past
  * mass_len are padding: far away and massless, so they add exactly zero.  Both ping-pong
  * position buffers are initialised because the epilogue only ever rewrites slots < mass_len.
+ * Packs [pack_first, pack_last) only: a GPU that received just its own particles converts just those.
  */
-__global__ void unpack_sources_kernel(const Particle *__restrict__ aos, uint32_t mass_len, uint32_t packs_pad,
-                                      float4 *xy0, float4 *xy1, float4 *gm) {
-    const uint32_t pk = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pk >= packs_pad) return;
+__global__ void unpack_sources_kernel(const Particle *__restrict__ aos, uint32_t mass_len, uint32_t pack_first,
+                                      uint32_t pack_last, float4 *xy0, float4 *xy1, float4 *gm) {
+    const uint32_t pk = pack_first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (pk >= pack_last) return;
     float x[4], y[4], g[4];
 #pragma unroll
     for (int l = 0; l < 4; l++) {

@@ -484,19 +484,94 @@ static void sync_all(SimPipeline *sim) {
     NB_CUDA(cudaSetDevice(sim->shards[0].device));
 }
 
-/* Every GPU receives the whole AoS array and derives its SoA state from it. */
+/* Sources [0, M) of shard q as a pack range (tile is a multiple of 4, so the range starts on a pack). */
+static bool source_packs_of_shard(const SimPipeline *sim, int q, size_t *p0, size_t *p1) {
+    uint32_t lo, hi;
+    particle_range_of_tiles(sim, sim->all_a0[q], sim->all_a1[q], sim->data.mass_len, &lo, &hi);
+    *p0 = lo / 4;
+    *p1 = ceil_div(hi, 4);
+    return hi > lo;
+}
+
+/* After an upload every GPU holds the source packs of its own massive particles: replicate them (both position
+ * buffers -- the pack that straddles mass_len carries padding lanes no step ever rewrites -- and G*m). */
+static void replicate_sources(SimPipeline *sim) {
+    if (sim->exchange == kExchangeNccl) {
+        NcclApi &api = nccl();
+        NB_NCCL(api.GroupStart());
+        for (Shard &sh : sim->shards) {
+            for (int q = 0; q < sim->total_shards; q++) {
+                size_t p0, p1;
+                if (!source_packs_of_shard(sim, q, &p0, &p1)) continue;
+                for (int b = 0; b < 2; b++) {
+                    float *xy = reinterpret_cast<float *>(sh.src_xy[b]) + p0 * 8;
+                    NB_NCCL(api.Broadcast(xy, xy, (p1 - p0) * 8, kNcclFloat, q, sh.comm, sh.stream));
+                }
+                float *gm = reinterpret_cast<float *>(sh.src_gm) + p0 * 4;
+                NB_NCCL(api.Broadcast(gm, gm, (p1 - p0) * 4, kNcclFloat, q, sh.comm, sh.stream));
+            }
+        }
+        NB_NCCL(api.GroupEnd());
+        return;
+    }
+    /* one process: the owner pushes its packs to every other GPU once its own conversion is done */
+    sync_all(sim);
+    for (Shard &src : sim->shards) {
+        size_t p0, p1;
+        if (!source_packs_of_shard(sim, src.global_index, &p0, &p1)) continue;
+        NB_CUDA(cudaSetDevice(src.device));
+        for (Shard &dst : sim->shards) {
+            if (&dst == &src) continue;
+            for (int b = 0; b < 2; b++)
+                NB_CUDA(cudaMemcpyPeerAsync(dst.src_xy[b] + p0 * 2, dst.device, src.src_xy[b] + p0 * 2, src.device,
+                                            (p1 - p0) * 2 * sizeof(float4), src.stream));
+            NB_CUDA(cudaMemcpyPeerAsync(dst.src_gm + p0, dst.device, src.src_gm + p0, src.device,
+                                        (p1 - p0) * sizeof(float4), src.stream));
+        }
+    }
+}
+
+/*
+ * SetSimulationData.  One GPU: the whole AoS array is copied and converted.  Several GPUs (in this process or
+ * across ranks): every GPU copies ONLY the particles it owns from PS (N x 32 B over PCIe in total, not per GPU),
+ * converts them, and the source packs (x, y, G*m of the massive particles, 12 B each) are then replicated
+ * GPU to GPU -- peer copies inside a process, NCCL broadcasts across processes.  Every rank passes the same
+ * array; a rank reads only its own ranges of it.
+ */
 static void upload(SimPipeline *sim, const Particle *ps) {
     const uint32_t N = sim->data.total_len, M = sim->data.mass_len;
     const Plan &pl = sim->plan;
+    const uint32_t data_packs = ceil_div(M, 4u);
     for (Shard &sh : sim->shards) {
         NB_CUDA(cudaSetDevice(sh.device));
-        NB_CUDA(cudaMemcpyAsync(sh.aos, ps, (size_t)N * sizeof(Particle), cudaMemcpyHostToDevice, sh.stream));
-        unpack_targets_kernel<<<ceil_div(N, 256), 256, 0, sh.stream>>>(sh.aos, N, sh.pos, sh.vel, sh.acc, sh.radius);
-        unpack_sources_kernel<<<ceil_div(pl.src_packs_pad, 128), 128, 0, sh.stream>>>(sh.aos, M, pl.src_packs_pad,
-                                                                                    sh.src_xy[0], sh.src_xy[1], sh.src_gm);
+        const uint32_t t0[2] = {sh.a0, sh.b0}, t1[2] = {sh.a1, sh.b1};
+        for (int r = 0; r < 2; r++) {
+            uint32_t lo = 0, hi = N;
+            if (sim->total_shards > 1) particle_range_of_tiles(sim, t0[r], t1[r], N, &lo, &hi);
+            else if (r == 1) break;
+            if (hi <= lo) continue;
+            NB_CUDA(cudaMemcpyAsync(sh.aos + lo, ps + lo, (size_t)(hi - lo) * sizeof(Particle), cudaMemcpyHostToDevice,
+                                    sh.stream));
+            unpack_targets_kernel<<<ceil_div(hi - lo, 256), 256, 0, sh.stream>>>(sh.aos + lo, hi - lo, sh.pos + lo,
+                                                                                  sh.vel + lo, sh.acc + lo, sh.radius + lo);
+            sim->kernels_launched++;
+        }
+        /* own source packs, and the padding packs past mass_len (they need no particle data) */
+        size_t p0 = 0, p1 = data_packs;
+        const bool own = sim->total_shards == 1 || source_packs_of_shard(sim, sh.global_index, &p0, &p1);
+        if (own && p1 > p0) {
+            unpack_sources_kernel<<<ceil_div((uint32_t)(p1 - p0), 128), 128, 0, sh.stream>>>(
+                sh.aos, M, (uint32_t)p0, (uint32_t)p1, sh.src_xy[0], sh.src_xy[1], sh.src_gm);
+            sim->kernels_launched++;
+        }
+        if (pl.src_packs_pad > data_packs) {
+            unpack_sources_kernel<<<ceil_div(pl.src_packs_pad - data_packs, 128), 128, 0, sh.stream>>>(
+                sh.aos, M, data_packs, pl.src_packs_pad, sh.src_xy[0], sh.src_xy[1], sh.src_gm);
+            sim->kernels_launched++;
+        }
         NB_CUDA(cudaGetLastError());
-        sim->kernels_launched += 2;
     }
+    if (sim->total_shards > 1) replicate_sources(sim);
     sim->cur = 0;
     sim->has_data = true;
     sync_all(sim); /* PS may be pageable and reused by the caller right after we return */
@@ -516,14 +591,15 @@ static void pack_own_ranges(SimPipeline *sim, Shard &sh) {
     }
 }
 
-static void download(SimPipeline *sim, Particle *ps) {
+/* LOCAL_ONLY: only the ranges owned by this process's GPUs are written to PS (no gather across ranks). */
+static void download(SimPipeline *sim, Particle *ps, bool local_only = false) {
     const uint32_t N = sim->data.total_len;
     NB_ASSERT(sim->has_data, "GetSimulationData before SetSimulationData");
     for (Shard &sh : sim->shards) {
         NB_CUDA(cudaSetDevice(sh.device));
         pack_own_ranges(sim, sh);
     }
-    if (sim->world > 1) {
+    if (sim->world > 1 && !local_only) {
         /* other processes own some ranges: all-gather the AoS ranges (32 B = 8 floats per particle) */
         NcclApi &api = nccl();
         NB_NCCL(api.GroupStart());
@@ -698,6 +774,26 @@ void DestroySimPipeline(SimPipeline *sim) { nb::destroy_pipeline(sim); }
 void SetSimulationData(SimPipeline *sim, const Particle *ps) { nb::upload(sim, ps); }
 
 void GetSimulationData(const SimPipeline *sim, Particle *ps) { nb::download(const_cast<SimPipeline *>(sim), ps); }
+
+void NbSimGetDataLocal(SimPipeline *sim, Particle *ps) { nb::download(sim, ps, true); }
+
+uint32_t NbSimLocalRanges(const SimPipeline *sim, uint32_t *out, uint32_t max_ranges) {
+    uint32_t n = 0;
+    for (const nb::Shard &sh : sim->shards) {
+        const uint32_t t0[2] = {sh.a0, sh.b0}, t1[2] = {sh.a1, sh.b1};
+        for (int r = 0; r < 2; r++) {
+            uint32_t lo, hi;
+            nb::particle_range_of_tiles(sim, t0[r], t1[r], sim->data.total_len, &lo, &hi);
+            if (hi <= lo) continue;
+            if (n < max_ranges) {
+                out[2 * n] = lo;
+                out[2 * n + 1] = hi;
+            }
+            n++;
+        }
+    }
+    return n;
+}
 
 void PerformSimUpdate(SimPipeline *sim, uint32_t n, float dt) {
     if (n == 0) return;

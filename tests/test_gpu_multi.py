@@ -46,3 +46,21 @@ def test_world_api_with_nbody_ngpus_env(nb, oracle, monkeypatch):
         two = w.particles()
         assert w.pipeline_info()["local_gpus"] == 2
     assert two.tobytes() == one.tobytes()
+
+
+@pytest.mark.parametrize("ranks,n", [(2, 50000), (2, 300000), (4, 100000), (8, 300000)])
+def test_one_rank_per_gpu_nccl_bitwise_equal_to_one_gpu(nb, ranks, n):
+    """torchrun, one process per GPU, NCCL position exchange, sharded upload (each rank is handed an array whose
+    foreign ranges are poisoned with NaN) and sharded read-back: tools/check_multirank.py."""
+    import os
+    import subprocess
+    import sys
+    if nb.device_count() < ranks:
+        pytest.skip(f"needs {ranks} GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={ranks}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29540 + ranks),
+           os.path.join(root, "tools", "check_multirank.py"), str(n), "3"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=root)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "bit-identical to 1 GPU" in out.stdout

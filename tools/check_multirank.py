@@ -29,19 +29,34 @@ def main():
     box = [nb.get_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(box, src=0)
     with nb.SimPipeline(len(arr), m, device=local, local_gpus=1, rank=rank, world=world, unique_id=box[0]) as sim:
-        sim.set_data(arr)
+        # sharded upload: a rank reads only the particles it owns out of the array it is given -- poison the rest
+        mine = sim.local_ranges()
+        poisoned = arr.copy()
+        own = np.zeros(len(arr), dtype=bool)
+        for lo, hi in mine:
+            own[lo:hi] = True
+        for k in ("px", "py", "vx", "vy", "mass", "radius"):
+            poisoned[k][~own] = np.nan
+        sim.set_data(poisoned)
         sim.update(steps, 0.01)
-        sharded = sim.get_data()
+        sharded = sim.get_data()                      # gathers the other ranks' particles
+        mine_only = np.zeros(len(arr), dtype=arr.dtype)
+        sim.get_data_local(mine_only)                     # sharded read-back: own ranges only, rest untouched
         ms = sim.last_step_ms()
+    local_ok = all(mine_only[lo:hi].tobytes() == sharded[lo:hi].tobytes() for lo, hi in mine) and \
+        not mine_only[~own].view(np.uint8).any() and sum(hi - lo for lo, hi in mine) > 0
+    flags = torch.tensor([int(local_ok)], device="cuda")
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    local_ok = bool(flags.item())
     ok = True
     if rank == 0:
         with nb.SimPipeline(len(arr), m, device=local, local_gpus=1) as one:
             one.set_data(arr)
             one.update(steps, 0.01)
             ref = one.get_data()
-        ok = sharded.tobytes() == ref.tobytes()
+        ok = sharded.tobytes() == ref.tobytes() and local_ok
         print(f"check_multirank: N={n} M={m} world={world} steps={steps}: "
-              f"{'bit-identical to 1 GPU' if ok else 'MISMATCH'}; last call {ms:.3f} ms", flush=True)
+              f"{'bit-identical to 1 GPU, sharded upload/read-back ok' if ok else 'MISMATCH'}; last call {ms:.3f} ms", flush=True)
     dist.barrier()
     dist.destroy_process_group()
     return 0 if ok else 1

@@ -50,7 +50,21 @@ def _rank_main(rank, world, port, n, galaxies, steps, dt, result_path):
     tile = info["tile_targets"]
     mine = _particle_ranges(ranges, rank, tile, len(w0))
 
+    # SetSimulationData, sharded: a rank reads only its own particles out of the array it is handed (the foreign
+    # ones are poisoned here), then the source data (x, y, mass of the massive particles) is replicated rank to rank
     arr = w0.copy()   # this rank's replica: own targets complete, foreign massive positions current
+    own = np.zeros(len(w0), dtype=bool)
+    for lo, hi in mine:
+        own[lo:hi] = True
+    for k in ("px", "py", "vx", "vy", "ax", "ay", "mass", "radius"):
+        arr[k][~own] = np.nan
+    for q in range(world):
+        q_lo, q_hi = min(ranges[q][0] * tile, m), min(ranges[q][1] * tile, m)
+        buf = torch.from_numpy(np.stack([arr[k][q_lo:q_hi] for k in ("px", "py", "mass")], axis=1).copy())
+        dist.broadcast(buf, src=q)
+        for c, k in enumerate(("px", "py", "mass")):
+            arr[k][q_lo:q_hi] = buf[:, c].numpy()
+    assert not np.isnan(arr["px"][:m]).any() and not np.isnan(arr["mass"][:m]).any()
     for _ in range(steps):
         new = arr.copy()
         for lo, hi in mine:                                      # "kernel": own targets vs all OLD sources
@@ -116,3 +130,20 @@ def test_plan_covers_all_tiles_once_and_is_independent_of_shard_count():
                 assert max(sizes) - min(sizes) <= 1
             assert info["tiles"] * info["tile_targets"] >= n
             assert info["slabs"] * info["slab_len"] >= m
+
+
+def test_source_packs_of_the_shards_partition_the_source_array():
+    """The sharded upload replicates, per shard, the packs [lo/4, ceil(min(hi, M)/4)) of its massive range:
+    together they must cover every data pack exactly once, whatever the shard count."""
+    import nbody_b200 as nb
+    for n, m in [(3000, 1504), (16384, 8086), (100000, 49944), (1048576, 523884), (1000003, 17), (5000, 4999)]:
+        for shards in (2, 3, 4, 8):
+            info, ranges = nb.plan(n, m, shards)
+            tile = info["tile_targets"]
+            assert tile % 4 == 0
+            packs = np.zeros((m + 3) // 4, dtype=np.int32)
+            for a0, a1, _, _ in ranges:
+                lo, hi = min(a0 * tile, m), min(a1 * tile, m)
+                if hi > lo:
+                    packs[lo // 4:(hi + 3) // 4] += 1
+            assert np.all(packs == 1), (n, m, shards)

@@ -150,7 +150,11 @@ enum {
     kAblateMufu = 4,     /* inv = r2 instead of rsqrt(r2): removes the 2 MUFU dispatch cycles          */
     kAblateAccRead = 5,  /* ax += f*f, ay += dy*dy: each accumulate reads 2 register pairs, not 3       */
     kAblateBoth = 6,
-    kAblateReduce = 7    /* every slab CTA integrates its own partial: no partial store, ticket, reduction */
+    kAblateReduce = 7,   /* every slab CTA integrates its own partial: no partial store, ticket, reduction */
+    /* packed arithmetic; the slab CTAs of a target tile form one thread-block cluster and add their partials
+     * through distributed shared memory instead of global memory + ticket (cluster_reduce.cuh).
+     * NBODY_VARIANT only: built and SASS-checked in round 1, not yet measured on a B200. */
+    kFormCluster = 8
 };
 
 template <int FORM>

@@ -30,6 +30,7 @@ struct Variant {
     const char *name;
     int threads, T, tjp, ns, minb, unr;
     double rel_cost; /* measured time per pair relative to the best variant at large N (0: not a plan candidate) */
+    bool cluster;    /* the nslab CTAs of a tile are one thread-block cluster (cluster_reduce.cuh): nslab <= 16 */
     size_t smem;
     const void *func;
     void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl);
@@ -45,17 +46,28 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     cfg.blockDim = dim3(THREADS);
     cfg.dynamicSmemBytes = step_smem_bytes<TJP, NS>();
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    unsigned na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    if (FORM == kFormCluster) { /* one cluster per target tile: its slab CTAs */
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = p.nslab;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        na++;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = na;
     NB_CUDA(cudaLaunchKernelEx(&cfg, step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>, p));
 }
 
 #define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR, FORM, REL)                                   \
     {                                                                                                 \
-        NAME, THREADS, T, TJP, NS, MINB, UNR, REL, step_smem_bytes<TJP, NS>(),                        \
+        NAME, THREADS, T, TJP, NS, MINB, UNR, REL, FORM == kFormCluster, step_smem_bytes<TJP, NS>(),  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>                                      \
     }
@@ -70,6 +82,9 @@ static const Variant kVariants[] = {
     NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked, 0.0),
     NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked, 0.0),
     NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2, kFormPacked, 0.0),
+    /* slab reduction through distributed shared memory; built in round 1, not yet measured (cluster_reduce.cuh) */
+    NB_VARIANT("c128x2", 128, 2, 64, 4, 6, 2, kFormCluster, 0.0),
+    NB_VARIANT("c128x4", 128, 4, 128, 4, 4, 2, kFormCluster, 0.0),
 };
 static const int kNumVariants = sizeof(kVariants) / sizeof(kVariants[0]);
 
@@ -110,6 +125,7 @@ static const uint32_t kMinTargetsPerGpu = 32768; /* below this a GPU is latency-
 static const uint32_t kMinSlabs = 16;       /* accuracy floor, see choose_slabs */
 static const uint32_t kMaxSlabSources = 16384;
 static const uint32_t kMinTiles = 48;       /* a variant needs this many target tiles to be a candidate */
+static const uint32_t kMaxClusterSlabs = 16; /* largest (non-portable) thread-block cluster on sm_100 */
 
 static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uint32_t slab_sources, int sm_count) {
     const double ctas = (double)tiles * nslab;
@@ -159,13 +175,15 @@ static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_s
         pl.nslab = 1;
         return weighted(1, unr);
     }
+    const uint32_t cap = pl.var->cluster ? kMaxClusterSlabs : 4096u;
     if (forced_slab_len) {
         pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
+        pl.slab_packs = std::max(pl.slab_packs, ceil_div(ceil_div(pl.src_packs, cap), unr) * unr);
         pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
         return weighted(pl.nslab, pl.slab_packs);
     }
     const uint32_t min_packs = 32; /* >= 128 sources per slab */
-    const uint32_t max_nslab = std::max(1u, std::min(4096u, pl.src_packs / min_packs));
+    const uint32_t max_nslab = std::max(1u, std::min(cap, pl.src_packs / min_packs));
     /* Accuracy floor: a register accumulator chain sums slab_len/2 terms, the reference's AVX build
      * M/8 (ref sim_cpu.c:165-189).  At least kMinSlabs slabs keeps our chains 4x shorter than the
      * reference's, so the CUDA result stays closer to FP64 than the reference is whatever the model
@@ -299,6 +317,10 @@ static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
     Plan &pl = sim->plan;
     plan_host(sim->data.total_len, sim->data.mass_len, sim->prop.multiProcessorCount, forced_slab, pl);
     NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+    if (pl.var->cluster) {
+        NB_ASSERT(pl.nslab <= kMaxClusterSlabs, "cluster variant %s with %u slabs", pl.var->name, pl.nslab);
+        if (pl.nslab > 8) NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    }
     int occ = 0;
     NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl.var->func, pl.var->threads, pl.var->smem));
     NB_ASSERT(occ >= pl.var->minb, "kernel variant %s: %d CTAs/SM resident, %d planned", pl.var->name, occ,
@@ -387,6 +409,8 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         NB_CUDA(cudaSetDevice(sh.device));
         if (l > 0) {
             NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+            if (pl.var->cluster && pl.nslab > 8)
+                NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         }
         if (cfg.stream && sim->local_gpus == 1) {
             sh.stream = (cudaStream_t)cfg.stream;

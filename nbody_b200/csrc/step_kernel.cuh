@@ -8,6 +8,7 @@
  */
 #pragma once
 
+#include "cluster_reduce.cuh"
 #include "force_kernel.cuh"
 
 namespace nb {
@@ -150,6 +151,11 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
             const uint32_t i = i0 + k * THREADS;
             if (i < p.total_len) integrate_store(p, i, a[k]);
         }
+        return;
+    }
+
+    if constexpr (FORM == kFormCluster) {
+        cluster_reduce_integrate<THREADS, T>(p, tile, a);
         return;
     }
 

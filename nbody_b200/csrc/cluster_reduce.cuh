@@ -10,8 +10,12 @@
  * partials of its 1/nslab share of the tile's targets straight out of the peers' shared memory and integrates
  * them.  No global traffic for the partials, no ticket, and the integration is spread over all CTAs of the tile.
  *
- * STATUS: selectable with NBODY_VARIANT=c128x2 / c128x4 only; compiled and inspected for sm_100a in round 1,
- * NOT yet run on a B200 (the round's GPU budget was spent) -- the planner never picks it.
+ * STATUS: measured on a B200 in round 1 (profiles/r01_cluster_variant_check.jsonl): bit-identical to the ticket path
+ * in every case, but SLOWER -- N = 4 000: 10.4 vs 8.1 us per step (8 slabs), N = 10 000: 28.1 vs 24.9 us, N = 16 384:
+ * 61.0 vs 48.6 us (16 slabs).  A cluster of 8-16 CTAs has to be co-scheduled on one GPC and every CTA keeps its slot
+ * until the slowest of the cluster has passed the second cluster barrier (each barrier also flushes L1:
+ * MEMBAR.ALL.GPU + CCTL.IVALL in the SASS), which costs more than the store + ticket + L2 reads it replaces.
+ * Kept selectable with NBODY_VARIANT=c128x2 / c128x4 as the record of that measurement; the planner never picks it.
  */
 #pragma once
 

@@ -153,7 +153,7 @@ enum {
     kAblateReduce = 7,   /* every slab CTA integrates its own partial: no partial store, ticket, reduction */
     /* packed arithmetic; the slab CTAs of a target tile form one thread-block cluster and add their partials
      * through distributed shared memory instead of global memory + ticket (cluster_reduce.cuh).
-     * NBODY_VARIANT only: built and SASS-checked in round 1, not yet measured on a B200. */
+     * NBODY_VARIANT only: measured slower than the ticket path at every size tried (cluster_reduce.cuh). */
     kFormCluster = 8
 };
 

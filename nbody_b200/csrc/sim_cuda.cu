@@ -82,7 +82,7 @@ static const Variant kVariants[] = {
     NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked, 0.0),
     NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked, 0.0),
     NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2, kFormPacked, 0.0),
-    /* slab reduction through distributed shared memory; built in round 1, not yet measured (cluster_reduce.cuh) */
+    /* slab reduction through distributed shared memory: bit-identical, measured slower (cluster_reduce.cuh) */
     NB_VARIANT("c128x2", 128, 2, 64, 4, 6, 2, kFormCluster, 0.0),
     NB_VARIANT("c128x4", 128, 4, 128, 4, 4, 2, kFormCluster, 0.0),
 };

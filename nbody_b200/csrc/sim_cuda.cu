@@ -123,11 +123,15 @@ static const double kWaveFixedClk = 8000.0; /* per wave of CTAs: first TMA round
 static const double kLaunchClk = 12000.0;   /* per launch */
 static const uint32_t kMinTargetsPerGpu = 32768; /* below this a GPU is latency-bound: not a split to plan for */
 static const uint32_t kMinSlabs = 16;       /* accuracy floor, see choose_slabs */
+static const uint32_t kShortWorldSources = 2048; /* ... except below this many sources, where the floor is */
+static const uint32_t kMinSlabSources = 256;     /*     slabs of this length (chains of 128 terms)             */
+static const double kReduceRoundClk = 1400.0; /* per 8 slabs: one dependent L2 round trip of the last-CTA reduction */
 static const uint32_t kMaxSlabSources = 16384;
 static const uint32_t kMinTiles = 48;       /* a variant needs this many target tiles to be a candidate */
 static const uint32_t kMaxClusterSlabs = 16; /* largest (non-portable) thread-block cluster on sm_100 */
 
-static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uint32_t slab_sources, int sm_count) {
+static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uint32_t slab_sources, int sm_count,
+                           bool short_world) {
     const double ctas = (double)tiles * nslab;
     const double slots = (double)v.minb * sm_count;
     const int warps = v.threads / 32;
@@ -135,6 +139,10 @@ static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uin
     auto occ_eff = [](int w) { return w >= 16 ? 1.0 : 0.7 + 0.3 * w / 16.0; };
     const double full = std::floor(ctas / slots), rem = ctas - full * slots;
     double t = kLaunchClk;
+    /* the tail of the launch is a last-CTA reduction: ceil(nslab / 8) dependent rounds of partial loads (measured at
+     * N = 4 000 with 16 tiles: 8 slabs 8.0 us, 13-16 slabs 8.8 us, profiles/r01_sweep_plan_smallN.txt; applied only
+     * to the short Worlds it was measured on -- larger ones keep the plans their parity runs were made with) */
+    if (nslab > 1 && short_world) t += kReduceRoundClk * std::ceil(nslab / 8.0);
     if (full > 0) t += full * (cta_pairs * v.minb / (kPairsPerClk * occ_eff(v.minb * warps)) + kWaveFixedClk);
     if (rem > 0) {
         const int k = (int)std::ceil(rem / sm_count);
@@ -165,7 +173,8 @@ static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_s
             const uint32_t g = (uint32_t)kGpus[q];
             /* a split is only worth planning for when every GPU keeps a throughput-bound share */
             if (g > 1 && (pl.ntiles < 2 * g || N / g < kMinTargetsPerGpu)) break;
-            cost += kWeight[q] * g * model_clocks(*pl.var, ceil_div(pl.ntiles, g), ns, sp * 4, sm_count);
+            cost += kWeight[q] * g * model_clocks(*pl.var, ceil_div(pl.ntiles, g), ns, sp * 4, sm_count,
+                                                  pl.src_packs * 4 < kShortWorldSources);
             wsum += kWeight[q];
         }
         return cost / wsum;
@@ -188,8 +197,13 @@ static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_s
      * M/8 (ref sim_cpu.c:165-189).  At least kMinSlabs slabs keeps our chains 4x shorter than the
      * reference's, so the CUDA result stays closer to FP64 than the reference is whatever the model
      * would prefer (measured at N = 50K: 6 slabs p99 1.5e-5 vs FP64, 45 slabs 2.2e-6, reference 1.9e-5);
-     * and no chain is longer than kMaxSlabSources/2 terms however large the World is. */
-    const uint32_t min_nslab = std::min(std::max(kMinSlabs, ceil_div(pl.src_packs * 4, kMaxSlabSources)), max_nslab);
+     * and no chain is longer than kMaxSlabSources/2 terms however large the World is.  Below
+     * kShortWorldSources the floor relaxes to slabs of kMinSlabSources: chains of 128 terms are short whatever
+     * their number (N = 4 003 fixture, FP32 emulation of both plans: p99 against FP64 5.8e-7 -> 8.0e-7). */
+    const uint32_t floor_slabs = pl.src_packs * 4 < kShortWorldSources
+                                     ? std::max(1u, ceil_div(pl.src_packs * 4, kMinSlabSources))
+                                     : kMinSlabs;
+    const uint32_t min_nslab = std::min(std::max(floor_slabs, ceil_div(pl.src_packs * 4, kMaxSlabSources)), max_nslab);
     double best = 1e300;
     uint32_t best_n = min_nslab;
     for (uint32_t n = min_nslab; n <= max_nslab; n++) {

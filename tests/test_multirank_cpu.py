@@ -147,3 +147,34 @@ def test_source_packs_of_the_shards_partition_the_source_array():
                 if hi > lo:
                     packs[lo // 4:(hi + 3) // 4] += 1
             assert np.all(packs == 1), (n, m, shards)
+
+
+def test_plan_invariants_on_random_sizes():
+    """Property test of the host-only planner (hypothesis): geometry covers the World, slab boundaries are whole
+    packs, shares are balanced, and nothing depends on the shard count."""
+    from hypothesis import given, settings, strategies as st
+    import nbody_b200 as nb
+
+    @settings(max_examples=150, deadline=None)
+    @given(n=st.integers(1, 6_000_000), frac=st.floats(0.0, 1.0), shards=st.sampled_from([1, 2, 3, 4, 8]))
+    def check(n, frac, shards):
+        m = min(n, int(n * frac))
+        info, ranges = nb.plan(n, m, shards)
+        tile = info["tile_targets"]
+        assert info["tiles"] * tile >= n > (info["tiles"] - 1) * tile
+        assert info["massive_tiles"] * tile >= m
+        assert info["slab_len"] % 16 == 0 and info["slabs"] >= 1
+        assert info["slabs"] * info["slab_len"] >= m
+        if m > 0:
+            assert (info["slabs"] - 1) * info["slab_len"] < m          # no empty slab
+            assert info["slab_len"] <= 16384                           # accuracy floor: chains of <= 8192 terms
+        one, _ = nb.plan(n, m, 1)
+        assert (one["variant"], one["tile_targets"], one["slab_len"], one["slabs"]) == \
+            (info["variant"], tile, info["slab_len"], info["slabs"])
+        covered = 0
+        for a0, a1, b0, b1 in ranges:
+            assert a0 <= a1 <= info["massive_tiles"] <= b0 <= b1 <= info["tiles"]
+            covered += (a1 - a0) + (b1 - b0)
+        assert covered == info["tiles"]
+
+    check()

@@ -130,6 +130,7 @@ def lib():
         # world.c extras
         "NbWorldPipeline": (vp, [vp]),
         "NbWorldMassLen": (u32, [vp]),
+        "NbWorldPrepareGPU": (None, [vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(L, name)

@@ -31,6 +31,7 @@
 /* world.c extras (not part of the reference header) */
 SimPipeline *NbWorldPipeline(World *w);
 uint32_t NbWorldMassLen(const World *w);
+void NbWorldPrepareGPU(World *w);
 
 typedef void (*UpdateFn)(World *, float, uint32_t);
 
@@ -40,8 +41,11 @@ static double seconds_now(void) {
     return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
 }
 
-/* warm-up call, then one timed call of STEPS steps; returns seconds per step */
+/* warm-up call, then one timed call of STEPS steps; returns seconds per step.  The device pipeline is created
+ * and the particles uploaded before the clock starts even with --warmup 0 (UpdateWorld_GPU(w, dt, 0) is a
+ * no-op that creates nothing, ref world.c:113). */
 static double time_path(World *w, UpdateFn update, uint32_t warmup, uint32_t steps, float dt) {
+    if (update == UpdateWorld_GPU) NbWorldPrepareGPU(w);
     update(w, dt, warmup);
     const double t0 = seconds_now();
     update(w, dt, steps);

@@ -6,7 +6,8 @@
  * is organised differently (one pass per concern over a small Galaxy record) but consumes libc
  * rand() in exactly the reference's order and evaluates every float expression with the same
  * operand order and precision, so with the same libc and seed the particles are bit-identical
- * (tests/test_galaxy.py checks this against the compiled reference and a golden fixture).
+ * (tests/test_host.py::test_make_galaxies_bit_identical_* check this against the compiled reference and the
+ * golden fixtures).
  * Compiled with -ffp-contract=off so no FMA sneaks into the float expressions.
  *
  * Draw order per call, one line per rand() (n = particles, g = galaxies):

@@ -263,6 +263,9 @@ struct SimPipeline {
     bool pdl = true;          /* programmatic dependent launch between chained steps */
     int cur = 0;              /* which src_xy buffer holds the current positions */
     bool has_data = false;
+    bool inert = false;       /* total_len == 0: no device state, every call is a no-op (the reference's CPU
+                                 path accepts an empty World, ref sim_cpu.c:109-111, and its world.c creates the
+                                 pipeline eagerly, ref world.c:52) */
     bool timed = false;       /* ev_begin/ev_end recorded at least once          */
     uint64_t kernels_launched = 0;
     cudaDeviceProp prop;
@@ -277,6 +280,23 @@ static int env_int(const char *name, int dflt) {
     if (!e || !*e) return dflt;
     return atoi(e);
 }
+
+/* The public entry points switch devices; the caller (a host program that may be on another device, e.g. torch)
+ * gets its current device back when they return. */
+struct DeviceGuard {
+    int prev = -1;
+    DeviceGuard() {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            (void)cudaGetLastError();
+            prev = -1;
+        }
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) (void)cudaSetDevice(prev);
+    }
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+};
 
 static void split_range(uint32_t first, uint32_t count, int parts, int idx, uint32_t *lo, uint32_t *hi) {
     *lo = first + (uint32_t)(((uint64_t)count * idx) / parts);
@@ -363,17 +383,22 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         memcpy(&cfg, cfg_in, std::min<size_t>(cfg_in->struct_size, sizeof cfg));
     }
 
+    NB_ASSERT(data.mass_len <= data.total_len, "mass_len %u > total_len %u", data.mass_len, data.total_len);
+    SimPipeline *sim = new SimPipeline();
+    sim->data = data;
+    sim->data.dt = 0.f;
+    if (data.total_len == 0) { /* legal on the reference's CPU path; nothing to allocate, nothing to run */
+        sim->inert = true;
+        memset(&sim->prop, 0, sizeof sim->prop);
+        memset(&sim->plan, 0, sizeof sim->plan);
+        return sim;
+    }
+
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
         NB_FAIL("no usable CUDA device (%s); this library has no CPU fallback for the GPU path",
                 e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
-    NB_ASSERT(data.mass_len <= data.total_len, "mass_len %u > total_len %u", data.mass_len, data.total_len);
-    NB_ASSERT(data.total_len > 0, "a World needs at least one particle");
-
-    SimPipeline *sim = new SimPipeline();
-    sim->data = data;
-    sim->data.dt = 0.f;
     const int first_dev = cfg.device >= 0 ? cfg.device : env_int("NBODY_DEVICE", 0);
     sim->local_gpus = cfg.local_gpus > 0 ? cfg.local_gpus : std::max(1, env_int("NBODY_NGPUS", 1));
     sim->world = std::max(1, cfg.world);
@@ -451,7 +476,8 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         sh.part = dev_alloc<float2>(pl.nslab > 1 ? (size_t)pl.nslab * ((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile : 1);
         sh.tile_cnt = dev_alloc<unsigned>(pl.ntiles);
         sh.scratch64 = dev_alloc<double>(8);
-        NB_CUDA(cudaMemset(sh.tile_cnt, 0, sizeof(unsigned) * pl.ntiles));
+        /* on the stream the step kernels run on: the legacy default stream does not order with it */
+        NB_CUDA(cudaMemsetAsync(sh.tile_cnt, 0, sizeof(unsigned) * pl.ntiles, sh.stream));
     }
     if (sim->exchange == kExchangePeerStore) {
         for (int a = 0; a < sim->local_gpus; a++) {
@@ -484,7 +510,10 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
             NB_NCCL(api.GroupEnd());
         }
     }
-    NB_CUDA(cudaSetDevice(first_dev));
+    for (Shard &sh : sim->shards) { /* creation-time initialisation done before anything else uses the buffers */
+        NB_CUDA(cudaSetDevice(sh.device));
+        NB_CUDA(cudaStreamSynchronize(sh.stream));
+    }
     return sim;
 }
 
@@ -503,7 +532,6 @@ static void destroy_pipeline(SimPipeline *sim) {
         if (sh.own_stream) cudaStreamDestroy(sh.stream);
         cudaStreamDestroy(sh.comm_stream);
     }
-    if (!sim->shards.empty()) cudaSetDevice(sim->shards[0].device);
     delete sim;
 }
 
@@ -519,7 +547,6 @@ static void sync_all(SimPipeline *sim) {
         NB_CUDA(cudaStreamSynchronize(sh.stream));
         NB_CUDA(cudaStreamSynchronize(sh.comm_stream));
     }
-    NB_CUDA(cudaSetDevice(sim->shards[0].device));
 }
 
 /* Sources [0, M) of shard q as a pack range (tile is a multiple of 4, so the range starts on a pack). */
@@ -794,7 +821,6 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         NB_CUDA(cudaEventRecord(sh.ev_end, sh.stream));
     }
     sim->timed = true;
-    NB_CUDA(cudaSetDevice(sim->shards[0].device));
 }
 
 }  // namespace nb
@@ -803,17 +829,38 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
 
 extern "C" {
 
-SimPipeline *CreateSimPipeline(WorldData data) { return nb::create_pipeline(data, nullptr); }
+SimPipeline *CreateSimPipeline(WorldData data) {
+    nb::DeviceGuard guard;
+    return nb::create_pipeline(data, nullptr);
+}
 
-SimPipeline *NbSimCreate(WorldData data, const NbSimConfig *cfg) { return nb::create_pipeline(data, cfg); }
+SimPipeline *NbSimCreate(WorldData data, const NbSimConfig *cfg) {
+    nb::DeviceGuard guard;
+    return nb::create_pipeline(data, cfg);
+}
 
-void DestroySimPipeline(SimPipeline *sim) { nb::destroy_pipeline(sim); }
+void DestroySimPipeline(SimPipeline *sim) {
+    nb::DeviceGuard guard;
+    nb::destroy_pipeline(sim);
+}
 
-void SetSimulationData(SimPipeline *sim, const Particle *ps) { nb::upload(sim, ps); }
+void SetSimulationData(SimPipeline *sim, const Particle *ps) {
+    if (sim->inert) return;
+    nb::DeviceGuard guard;
+    nb::upload(sim, ps);
+}
 
-void GetSimulationData(const SimPipeline *sim, Particle *ps) { nb::download(const_cast<SimPipeline *>(sim), ps); }
+void GetSimulationData(const SimPipeline *sim, Particle *ps) {
+    if (sim->inert) return;
+    nb::DeviceGuard guard;
+    nb::download(const_cast<SimPipeline *>(sim), ps);
+}
 
-void NbSimGetDataLocal(SimPipeline *sim, Particle *ps) { nb::download(sim, ps, true); }
+void NbSimGetDataLocal(SimPipeline *sim, Particle *ps) {
+    if (sim->inert) return;
+    nb::DeviceGuard guard;
+    nb::download(sim, ps, true);
+}
 
 uint32_t NbSimLocalRanges(const SimPipeline *sim, uint32_t *out, uint32_t max_ranges) {
     uint32_t n = 0;
@@ -834,20 +881,27 @@ uint32_t NbSimLocalRanges(const SimPipeline *sim, uint32_t *out, uint32_t max_ra
 }
 
 void PerformSimUpdate(SimPipeline *sim, uint32_t n, float dt) {
-    if (n == 0) return;
+    if (n == 0 || sim->inert) return;
+    nb::DeviceGuard guard;
     nb::step_async(sim, n, dt);
     nb::sync_all(sim); /* synchronous like the reference's fence wait, ref sim_gpu.c:352-353 */
 }
 
 void NbSimStepAsync(SimPipeline *sim, uint32_t n, float dt) {
-    if (n == 0) return;
+    if (n == 0 || sim->inert) return;
+    nb::DeviceGuard guard;
     nb::step_async(sim, n, dt);
 }
 
-void NbSimSynchronize(SimPipeline *sim) { nb::sync_all(sim); }
+void NbSimSynchronize(SimPipeline *sim) {
+    if (sim->inert) return;
+    nb::DeviceGuard guard;
+    nb::sync_all(sim);
+}
 
 float NbSimLastStepMs(SimPipeline *sim) {
     if (!sim->timed) return 0.f;
+    nb::DeviceGuard guard;
     float worst = 0.f;
     for (nb::Shard &sh : sim->shards) {
         NB_CUDA(cudaSetDevice(sh.device));
@@ -856,7 +910,6 @@ float NbSimLastStepMs(SimPipeline *sim) {
         NB_CUDA(cudaEventElapsedTime(&ms, sh.ev_begin, sh.ev_end));
         worst = ms > worst ? ms : worst;
     }
-    NB_CUDA(cudaSetDevice(sim->shards[0].device));
     return worst;
 }
 
@@ -907,6 +960,13 @@ int32_t NbSimDeviceCount(void) {
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     memset(out, 0, sizeof *out);
+    if (sim->inert) { /* an empty World: nothing on any device */
+        strncpy(out->device_name, "(none: empty World)", sizeof out->device_name - 1);
+        out->device = -1;
+        out->world = 1;
+        out->kernels_launched = 0;
+        return;
+    }
     strncpy(out->device_name, sim->prop.name, sizeof out->device_name - 1);
     out->device = sim->shards[0].device;
     out->local_gpus = sim->local_gpus;
@@ -937,6 +997,7 @@ static void refresh_aos_on_first_gpu(SimPipeline *sim) {
     const uint32_t N = sim->data.total_len;
     nb::Shard &sh = sim->shards[0];
     NB_ASSERT(sim->has_data, "no particle data on the device yet");
+    NB_CUDA(cudaSetDevice(sh.device));
     if (sim->total_shards > 1) {
         Particle *tmp = (Particle *)NbSimHostAlloc((size_t)N * sizeof(Particle));
         nb::download(sim, tmp);
@@ -951,9 +1012,15 @@ static void refresh_aos_on_first_gpu(SimPipeline *sim) {
 }
 
 void NbSimDiagnostics(SimPipeline *sim, double *out7) {
+    if (sim->inert) {
+        memset(out7, 0, 7 * sizeof(double));
+        return;
+    }
+    nb::DeviceGuard guard;
     const uint32_t N = sim->data.total_len;
     nb::Shard &sh = sim->shards[0];
     refresh_aos_on_first_gpu(sim);
+    NB_CUDA(cudaSetDevice(sh.device));
     NB_CUDA(cudaMemsetAsync(sh.scratch64, 0, 7 * sizeof(double), sh.stream));
     nb::diagnostics_kernel<<<nb::ceil_div(N, 256), 256, 0, sh.stream>>>(sh.aos, N, sim->data.mass_len, sh.scratch64);
     NB_CUDA(cudaGetLastError());
@@ -963,9 +1030,16 @@ void NbSimDiagnostics(SimPipeline *sim, double *out7) {
 }
 
 void NbSimFitCamera(SimPipeline *sim, int32_t width, int32_t height, float *target_x, float *target_y, float *zoom) {
+    if (sim->inert) {
+        *target_x = *target_y = 0.f;
+        *zoom = 1.f;
+        return;
+    }
+    nb::DeviceGuard guard;
     const uint32_t N = sim->data.total_len;
     nb::Shard &sh = sim->shards[0];
     refresh_aos_on_first_gpu(sim);
+    NB_CUDA(cudaSetDevice(sh.device));
     int *d = nb::dev_alloc<int>(4);
     const int init[4] = {nb::float_to_ordered_host(INFINITY), nb::float_to_ordered_host(INFINITY),
                          nb::float_to_ordered_host(-INFINITY), nb::float_to_ordered_host(-INFINITY)};
@@ -991,8 +1065,14 @@ void NbSimRenderRGBA(SimPipeline *sim, int32_t width, int32_t height, float targ
     NB_ASSERT(width > 0 && height > 0 && (int64_t)width * height <= (1 << 28), "bad image size %d x %d", width, height);
     const uint32_t N = sim->data.total_len;
     const uint32_t pixels = (uint32_t)width * (uint32_t)height;
+    if (sim->inert) { /* background only */
+        for (uint32_t k = 0; k < pixels; k++) rgba[4 * k] = rgba[4 * k + 1] = rgba[4 * k + 2] = 22, rgba[4 * k + 3] = 255;
+        return;
+    }
+    nb::DeviceGuard guard;
     nb::Shard &sh = sim->shards[0];
     refresh_aos_on_first_gpu(sim);
+    NB_CUDA(cudaSetDevice(sh.device));
     unsigned *winner = nb::dev_alloc<unsigned>(pixels);
     uchar4 *img = nb::dev_alloc<uchar4>(pixels);
     NB_CUDA(cudaMemsetAsync(winner, 0, (size_t)pixels * sizeof(unsigned), sh.stream));
@@ -1011,6 +1091,7 @@ void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out) {
     NB_ASSERT(first <= last && last <= sim->data.total_len, "bad target range [%u, %u)", first, last);
     NB_ASSERT(sim->total_shards == 1, "NbSimAccF64 is a single-GPU diagnostic");
     if (first == last) return;
+    nb::DeviceGuard guard;
     nb::Shard &sh = sim->shards[0];
     NB_CUDA(cudaSetDevice(sh.device));
     double *d = nb::dev_alloc<double>(2 * (size_t)(last - first));

@@ -162,13 +162,19 @@ def test_pair_loop_schedule_is_the_measured_one(nb):
         pytest.skip("cuobjdump unavailable")
     want = json.load(open(fpmod.FINGERPRINT))
     got = fpmod.fingerprint(nb.LIB_PATH)
+    meta = want.get("_meta", {})
     for name, w in want.items():
+        if name.startswith("_"):
+            continue
         g = got[name]
         # per 32 pairs (two packs of 4 sources x 4 targets): 9 packed FP32 instructions and 2 MUFU per 2 pairs
         assert g["loop_f32x2"] == w["loop_f32x2"] and g["loop_mufu"] == w["loop_mufu"], (name, g)
+        # This assertion is MEANT to fail on any nvcc/ptxas or kernel-source change that reorders the loop: the
+        # committed timings belong to the recorded schedule.  It is a prompt to re-measure, not a correctness failure.
         assert g["loop_sha1"] == w["loop_sha1"], (
-            f"{name}: ptxas scheduled the pair loop differently; re-measure on a B200, then "
-            "python tools/sass_fingerprint.py --update")
+            f"{name}: ptxas scheduled the pair loop differently from the schedule the committed numbers were "
+            f"measured with (recorded with CUDA toolkit '{meta.get('toolkit', 'unknown')}', this build uses "
+            f"'{fpmod.toolkit_version()}').  Procedure: {meta.get('procedure', 're-measure on a B200, then python tools/sass_fingerprint.py --update')}")
 
 
 def test_device_count_without_gpu_is_zero_or_more(nb):
@@ -204,3 +210,23 @@ def test_c_program_against_the_world_api(nb, tmp_path):
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count(" ok") == 7
+
+
+def test_empty_pipeline_is_inert_through_the_reference_seam(nb):
+    """The reference's own world.c creates the pipeline eagerly in CreateWorld (ref world.c:52), also for an empty
+    World that its CPU path accepts (ref sim_cpu.c:109-111): CreateSimPipeline(total_len == 0) must return a
+    pipeline on which Set/Get/Perform are no-ops -- without touching any device, so this runs on the build box."""
+    import ctypes as C
+    L = nb.lib()
+    sim = L.CreateSimPipeline(nb.api.WorldData(0, 0, 0.0))
+    assert sim
+    L.SetSimulationData(sim, None)
+    L.PerformSimUpdate(sim, 3, 0.01)
+    L.NbSimStepAsync(sim, 2, 0.01)
+    L.NbSimSynchronize(sim)
+    L.GetSimulationData(sim, None)
+    assert L.NbSimLastStepMs(sim) == 0.0
+    info = nb.api.SimInfo()
+    L.NbSimGetInfo(sim, C.byref(info))
+    assert info.total_len == 0 and info.kernels_launched == 0
+    L.DestroySimPipeline(sim)

@@ -67,6 +67,17 @@ def pair_loop(ops):
     return ops[start:end + 1]
 
 
+def toolkit_version():
+    """`release 12.9, V12.9.86` of the nvcc that would build the library (ptxas ships with it)."""
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    try:
+        out = subprocess.run([nvcc, "--version"], capture_output=True, text=True).stdout
+    except OSError:
+        return "unknown"
+    m = re.search(r"release [0-9.]+, V[0-9.]+", out)
+    return m.group(0) if m else "unknown"
+
+
 def fingerprint(lib):
     fp = {}
     for name, sym in KERNELS.items():
@@ -97,12 +108,17 @@ def main():
     fp = fingerprint(args.lib)
     print(json.dumps(fp, indent=1))
     if args.update:
+        fp["_meta"] = {"toolkit": toolkit_version(),
+                       "procedure": "after an intended kernel or toolkit change: make tune && gpurun "
+                                    "'TUNE_SET=ship tools/bin/tune sweep 1048576 523884 37' (and python bench.py), "
+                                    "compare with profiles/*_tune_sweep*.txt / DESIGN.md section 7, then "
+                                    "python tools/sass_fingerprint.py --update and commit the new numbers"}
         with open(FINGERPRINT, "w") as f:
             json.dump(fp, f, indent=1)
             f.write("\n")
     elif os.path.exists(FINGERPRINT):
         want = json.load(open(FINGERPRINT))
-        bad = [k for k in fp if want.get(k, {}).get("loop_sha1") != fp[k]["loop_sha1"]]
+        bad = [k for k in fp if not k.startswith("_") and want.get(k, {}).get("loop_sha1") != fp[k]["loop_sha1"]]
         if bad:
             sys.exit("schedule of the pair loop changed for: " + ", ".join(bad))
 

@@ -123,6 +123,8 @@ typedef struct NbSimInfo {
     uint32_t tiles_local;   /* target tiles computed by this process      */
     uint64_t kernels_launched; /* kernels this pipeline has launched so far */
     uint64_t pairs_per_step;   /* total_len * mass_len                      */
+    uint32_t group_slabs;   /* consecutive slabs one CTA walks (1: a CTA per slab); partials per target = */
+                            /* ceil(slabs / group_slabs)                                                  */
 } NbSimInfo;
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);
@@ -140,6 +142,10 @@ typedef struct NbSimPlanInfo {
     uint32_t slab_len;       /* sources per partial-sum slab                      */
     uint32_t slabs;          /* slabs per tile; fixes the summation order         */
     uint32_t ctas_per_sm;    /* resident CTAs per SM the plan assumes             */
+    uint32_t group_slabs;    /* consecutive slabs one CTA walks and sums in slab order itself (1: one CTA per  */
+                             /* slab).  > 1 only where one partial per (slab, target) would exceed the budget */
+    uint32_t groups;         /* CTAs per tile = partial sums per target = ceil(slabs / group_slabs); they are */
+                             /* added in group order                                                           */
 } NbSimPlanInfo;
 
 void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm_count, NbSimPlanInfo *out,

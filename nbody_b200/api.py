@@ -47,6 +47,8 @@ class SimPlanInfo(C.Structure):  # include/nbody_sim.h NbSimPlanInfo
         ("slab_len", C.c_uint32),
         ("slabs", C.c_uint32),
         ("ctas_per_sm", C.c_uint32),
+        ("group_slabs", C.c_uint32),
+        ("groups", C.c_uint32),
     ]
 
 
@@ -70,6 +72,7 @@ class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
         ("tiles_local", C.c_uint32),
         ("kernels_launched", C.c_uint64),
         ("pairs_per_step", C.c_uint64),
+        ("group_slabs", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -74,6 +74,10 @@ struct StepParams {
     const float4 *src_gm;     /* [src_packs_pad]     G*mass of 4 sources                  */
     float *dst_xy[kMaxDst];   /* next-step source buffers (as floats), self first         */
     int ndst;
+    uint32_t fold_tiles;      /* grouped kernels only (step_kernel GROUPED): source tiles per slab; a CTA walks */
+                              /* several consecutive slabs and folds each slab's sum into a running sum.  Sits   */
+                              /* in what used to be alignment padding: the layout the other kernels see is       */
+                              /* unchanged (an extra parameter elsewhere re-ordered their pair loop)  */
     float2 *pos;              /* [total_len] target positions, updated in place           */
     float2 *vel;              /* [total_len]                                              */
     float2 *acc;              /* [total_len]                                              */
@@ -84,8 +88,8 @@ struct StepParams {
     uint32_t total_len, mass_len;
     uint32_t part_stride;     /* targets this GPU computes, in whole tiles                */
     uint32_t src_packs_pad;   /* source packs incl. padding, multiple of TJP              */
-    uint32_t slab_packs;      /* packs per slab (multiple of the inner unroll)            */
-    uint32_t nslab;
+    uint32_t slab_packs;      /* packs per CTA: one slab, or one group of slabs (GROUPED) */
+    uint32_t nslab;           /* CTAs per target tile: slabs, or groups of slabs (GROUPED) */
     uint32_t tile_first;      /* first target tile of this launch                         */
     float dt;
 };

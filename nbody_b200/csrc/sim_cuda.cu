@@ -34,9 +34,13 @@ struct Variant {
     size_t smem;
     const void *func;
     void (*launch)(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl);
+    /* the same kernel walking a group of slabs per CTA (step_kernel GROUPED); null where it is not built */
+    size_t smem_grouped;
+    const void *func_grouped;
+    void (*launch_grouped)(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl);
 };
 
-template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM>
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM, bool GROUPED = false>
 static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
     /* Programmatic dependent launch: the next step's CTAs may become resident while this step's last
      * CTAs drain; they run their prologue and block in griddepcontrol.wait until this grid has
@@ -44,7 +48,7 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(THREADS);
-    cfg.dynamicSmemBytes = step_smem_bytes<TJP, NS>();
+    cfg.dynamicSmemBytes = GROUPED ? step_smem_bytes_grouped<THREADS, T, TJP, NS>() : step_smem_bytes<TJP, NS>();
     cfg.stream = st;
     cudaLaunchAttribute attr[2];
     unsigned na = 0;
@@ -62,22 +66,32 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    NB_CUDA(cudaLaunchKernelEx(&cfg, step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>, p));
+    NB_CUDA(cudaLaunchKernelEx(&cfg, step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM, GROUPED>, p));
 }
 
 #define NB_VARIANT(NAME, THREADS, T, TJP, NS, MINB, UNR, FORM, REL)                                   \
     {                                                                                                 \
         NAME, THREADS, T, TJP, NS, MINB, UNR, REL, FORM == kFormCluster, step_smem_bytes<TJP, NS>(),  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>                                      \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr                 \
+    }
+/* a plan candidate: also built as a GROUPED kernel for Worlds whose per-slab partials exceed the budget */
+#define NB_VARIANT_G(NAME, THREADS, T, TJP, NS, MINB, UNR, REL)                                              \
+    {                                                                                                        \
+        NAME, THREADS, T, TJP, NS, MINB, UNR, REL, false, step_smem_bytes<TJP, NS>(),                        \
+            (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked>,                          \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked>,                                     \
+            step_smem_bytes_grouped<THREADS, T, TJP, NS>(),                                                  \
+            (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>,                    \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>                                \
     }
 
 static const Variant kVariants[] = {
     /* plan candidates, with their measured cost per pair relative to t512x4 (profiles/r01_tune_sweep*.txt) */
-    NB_VARIANT("t512x4", 512, 4, 128, 4, 1, 2, kFormPacked, 1.000), /* 2048 targets per CTA, 1 CTA/SM  */
-    NB_VARIANT("t256x4", 256, 4, 128, 4, 2, 2, kFormPacked, 1.010), /* 1024 targets per CTA            */
-    NB_VARIANT("t128x4", 128, 4, 128, 4, 4, 2, kFormPacked, 1.025), /* 512 targets per CTA             */
-    NB_VARIANT("t128x2", 128, 2, 64, 4, 6, 2, kFormPacked, 1.065),  /* 256 targets per CTA, small N    */
+    NB_VARIANT_G("t512x4", 512, 4, 128, 4, 1, 2, 1.000), /* 2048 targets per CTA, 1 CTA/SM  */
+    NB_VARIANT_G("t256x4", 256, 4, 128, 4, 2, 2, 1.010), /* 1024 targets per CTA            */
+    NB_VARIANT_G("t128x4", 128, 4, 128, 4, 4, 2, 1.025), /* 512 targets per CTA             */
+    NB_VARIANT_G("t128x2", 128, 2, 64, 4, 6, 2, 1.065),  /* 256 targets per CTA, small N    */
     /* selectable with NBODY_VARIANT only */
     NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked, 0.0),
     NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked, 0.0),
@@ -98,7 +112,9 @@ struct Plan {
     uint32_t n_pad;          /* ntiles * tile                                       */
     uint32_t src_packs;      /* ceil(mass_len / 4)                                  */
     uint32_t src_packs_pad;  /* rounded up to the smem tile                         */
-    uint32_t slab_packs, nslab;
+    uint32_t slab_packs, nslab; /* the slabs: they fix the summation order                              */
+    uint32_t group_slabs;       /* consecutive slabs one CTA walks (1: one CTA per slab)                */
+    uint32_t ngroups;           /* CTAs per target tile = ceil(nslab / group_slabs) = partials per target */
     int ctas_per_sm;
 };
 
@@ -162,29 +178,80 @@ static void set_geometry(Plan &pl, const Variant *v, uint32_t N, uint32_t M) {
     pl.src_packs_pad = std::max(1u, ceil_div(pl.src_packs, (uint32_t)v->tjp)) * v->tjp;
 }
 
-/* Best slab count for one variant; returns the weighted model time (GPU-clocks summed over GPUs). */
-static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
-    const uint32_t unr = 4; /* slab granularity in packs: a multiple of every variant's unroll */
+/* Model time of a plan with NS CTAs per target tile of SP packs each, weighted over the GPU counts a World may be
+ * split over (GPU-clocks summed over GPUs). */
+static double weighted_cost(const Plan &pl, uint32_t N, int sm_count, uint32_t ns, uint32_t sp) {
     static const int kGpus[4] = {1, 2, 4, 8};
     static const double kWeight[4] = {4.0, 1.0, 1.0, 2.0};
-    auto weighted = [&](uint32_t ns, uint32_t sp) {
-        double cost = 0.0, wsum = 0.0;
-        for (int q = 0; q < 4; q++) {
-            const uint32_t g = (uint32_t)kGpus[q];
-            /* a split is only worth planning for when every GPU keeps a throughput-bound share */
-            if (g > 1 && (pl.ntiles < 2 * g || N / g < kMinTargetsPerGpu)) break;
-            cost += kWeight[q] * g * model_clocks(*pl.var, ceil_div(pl.ntiles, g), ns, sp * 4, sm_count,
-                                                  pl.src_packs * 4 < kShortWorldSources);
-            wsum += kWeight[q];
+    double cost = 0.0, wsum = 0.0;
+    for (int q = 0; q < 4; q++) {
+        const uint32_t g = (uint32_t)kGpus[q];
+        /* a split is only worth planning for when every GPU keeps a throughput-bound share */
+        if (g > 1 && (pl.ntiles < 2 * g || N / g < kMinTargetsPerGpu)) break;
+        cost += kWeight[q] * g * model_clocks(*pl.var, ceil_div(pl.ntiles, g), ns, sp * 4, sm_count,
+                                              pl.src_packs * 4 < kShortWorldSources);
+        wsum += kWeight[q];
+    }
+    return cost / wsum;
+}
+
+/* Bytes the slab partials of ONE GPU running the whole World may take (nslab x targets x 8 B).  A constant, not
+ * the free memory of the device at hand: the plan fixes the summation order and must be a function of (N, M)
+ * only.  NBODY_PART_BUDGET (bytes) overrides it -- for tests, which force slab groups at small N with it. */
+static const uint64_t kPartBudgetBytes = 1ull << 30;
+static uint64_t part_budget_bytes() {
+    const char *e = getenv("NBODY_PART_BUDGET");
+    if (e && *e) return std::max<uint64_t>(1, strtoull(e, nullptr, 10));
+    return kPartBudgetBytes;
+}
+
+/*
+ * Slab groups: bound the partial buffer.  The slab count grows with M (no accumulator chain longer than
+ * kMaxSlabSources / 2 terms), so one partial per (slab, target) is nslab x N x 8 B = O(N x M): 310 MB at N = 1M,
+ * 4.3 GB at 4M, 69 GB at 16M.  Past the budget a CTA walks `group_slabs` consecutive slabs and adds their sums in
+ * slab order itself (step_kernel GROUPED); only ngroups = ceil(nslab / group_slabs) partials per target reach
+ * memory.  Slabs become whole source tiles for this; the number of groups is chosen by the same timing model as
+ * the slab count.  Returns the model cost of the final plan.
+ */
+static double group_slabs(Plan &pl, uint32_t N, int sm_count, double cost) {
+    pl.group_slabs = 1;
+    pl.ngroups = pl.nslab;
+    const uint64_t per_partial = (uint64_t)pl.n_pad * sizeof(float2);
+    const uint64_t budget = part_budget_bytes();
+    if (pl.nslab <= 1 || pl.var->func_grouped == nullptr || (uint64_t)pl.nslab * per_partial <= budget) return cost;
+    const uint32_t tjp = (uint32_t)pl.var->tjp;
+    const uint32_t sp = std::max(tjp, pl.slab_packs / tjp * tjp);
+    const uint32_t ns = ceil_div(pl.src_packs, sp);
+    const uint32_t max_groups = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ns, budget / per_partial));
+    double best = 1e300;
+    uint32_t best_gs = ns;
+    for (uint32_t g = max_groups; g >= 1; g--) { /* on near ties: more, shorter CTAs */
+        const uint32_t gs = ceil_div(ns, g);
+        const uint32_t groups = ceil_div(ns, gs);
+        if (groups != g) continue;
+        const double c = weighted_cost(pl, N, sm_count, groups, gs * sp);
+        if (c < best * 0.999) {
+            best = c;
+            best_gs = gs;
         }
-        return cost / wsum;
-    };
+    }
+    pl.slab_packs = sp;
+    pl.nslab = ns;
+    pl.group_slabs = best_gs;
+    pl.ngroups = ceil_div(ns, best_gs);
+    return best;
+}
+
+/* Best slab count for one variant; returns the weighted model time (GPU-clocks summed over GPUs). */
+static double choose_slabs_ungrouped(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
+    const uint32_t unr = 4; /* slab granularity in packs: a multiple of every variant's unroll */
+    auto weighted = [&](uint32_t ns, uint32_t sp) { return weighted_cost(pl, N, sm_count, ns, sp); };
     if (pl.src_packs == 0) {
         pl.slab_packs = unr;
         pl.nslab = 1;
         return weighted(1, unr);
     }
-    const uint32_t cap = pl.var->cluster ? kMaxClusterSlabs : 4096u;
+    const uint32_t cap = pl.var->cluster ? kMaxClusterSlabs : 65536u; /* slabs per tile (grouped beyond the budget) */
     if (forced_slab_len) {
         pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
         pl.slab_packs = std::max(pl.slab_packs, ceil_div(ceil_div(pl.src_packs, cap), unr) * unr);
@@ -219,6 +286,11 @@ static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_s
     pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
     if (best >= 1e300) best = weighted(pl.nslab, pl.slab_packs); /* no count in range divides evenly */
     return best;
+}
+
+static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
+    const double cost = choose_slabs_ungrouped(pl, N, sm_count, forced_slab_len);
+    return group_slabs(pl, N, sm_count, cost);
 }
 
 static const Variant *forced_variant() {
@@ -347,18 +419,22 @@ static void shard_tiles(const Plan &pl, int S, int q, uint32_t *a0, uint32_t *a1
     split_range(pl.mtiles, pl.ntiles - pl.mtiles, S, q, b0, b1);
 }
 
+/* the kernel a plan runs: the variant itself, or its GROUPED build when a CTA walks several slabs */
+static const void *plan_func(const Plan &pl) { return pl.group_slabs > 1 ? pl.var->func_grouped : pl.var->func; }
+static size_t plan_smem(const Plan &pl) { return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem; }
+
 static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
     Plan &pl = sim->plan;
     plan_host(sim->data.total_len, sim->data.mass_len, sim->prop.multiProcessorCount, forced_slab, pl);
-    NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+    NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem(pl)));
     if (pl.var->cluster) {
         NB_ASSERT(pl.nslab <= kMaxClusterSlabs, "cluster variant %s with %u slabs", pl.var->name, pl.nslab);
         if (pl.nslab > 8) NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     }
     int occ = 0;
-    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pl.var->func, pl.var->threads, pl.var->smem));
-    NB_ASSERT(occ >= pl.var->minb, "kernel variant %s: %d CTAs/SM resident, %d planned", pl.var->name, occ,
-              pl.var->minb);
+    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, plan_func(pl), pl.var->threads, plan_smem(pl)));
+    NB_ASSERT(occ >= pl.var->minb, "kernel variant %s%s: %d CTAs/SM resident, %d planned", pl.var->name,
+              pl.group_slabs > 1 ? " (grouped)" : "", occ, pl.var->minb);
 }
 
 }  // namespace nb
@@ -447,7 +523,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         sh.b0 = sim->all_b0[sh.global_index]; sh.b1 = sim->all_b1[sh.global_index];
         NB_CUDA(cudaSetDevice(sh.device));
         if (l > 0) {
-            NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+            NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem(pl)));
             if (pl.var->cluster && pl.nslab > 8)
                 NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         }
@@ -464,6 +540,18 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         NB_CUDA(cudaEventCreateWithFlags(&sh.ev_comm, cudaEventDisableTiming));
         NB_CUDA(cudaEventCreateWithFlags(&sh.ev_step, cudaEventDisableTiming));
         const size_t N = data.total_len;
+        /* one readable failure instead of a bare cudaErrorMemoryAllocation from somewhere in the middle */
+        const size_t own_targets = (size_t)((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile;
+        const size_t part_bytes = pl.ngroups > 1 ? (size_t)pl.ngroups * own_targets * sizeof(float2) : 0;
+        const size_t need = N * (sizeof(Particle) + 3 * sizeof(float2) + sizeof(float)) +
+                            (size_t)pl.src_packs_pad * 5 * sizeof(float4) + part_bytes + pl.ntiles * sizeof(unsigned);
+        size_t free_b = 0, total_b = 0;
+        NB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        NB_ASSERT(need + (64u << 20) <= free_b,
+                  "device %d: a World of %u particles (%u massive) needs %.2f GB of device memory (%.2f GB of it slab "
+                  "partials: %u per target), %.2f GB are free of %.2f GB",
+                  sh.device, data.total_len, data.mass_len, need * 1e-9, part_bytes * 1e-9, pl.ngroups, free_b * 1e-9,
+                  total_b * 1e-9);
         sh.aos = dev_alloc<Particle>(N);
         sh.src_xy[0] = dev_alloc<float4>((size_t)pl.src_packs_pad * 2);
         sh.src_xy[1] = dev_alloc<float4>((size_t)pl.src_packs_pad * 2);
@@ -473,7 +561,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         sh.acc = dev_alloc<float2>(N);
         sh.radius = dev_alloc<float>(N);
         /* partial sums only for the tiles this GPU computes: [nslab][own tiles * tile] */
-        sh.part = dev_alloc<float2>(pl.nslab > 1 ? (size_t)pl.nslab * ((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile : 1);
+        sh.part = dev_alloc<float2>(pl.ngroups > 1 ? (size_t)pl.ngroups * own_targets : 1);
         sh.tile_cnt = dev_alloc<unsigned>(pl.ntiles);
         sh.scratch64 = dev_alloc<double>(8);
         /* on the stream the step kernels run on: the legacy default stream does not order with it */
@@ -723,7 +811,9 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
     p->total_len = sim->data.total_len; p->mass_len = sim->data.mass_len;
     p->part_stride = ((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile;
     p->src_packs_pad = pl.src_packs_pad;
-    p->slab_packs = pl.slab_packs; p->nslab = pl.nslab;
+    /* the kernel's "slab" is what one CTA walks: a slab, or a group of slabs it folds itself (GROUPED) */
+    p->slab_packs = pl.slab_packs * pl.group_slabs; p->nslab = pl.ngroups;
+    p->fold_tiles = pl.group_slabs > 1 ? pl.slab_packs / (uint32_t)pl.var->tjp : 0;
     p->dt = dt;
 }
 
@@ -740,9 +830,10 @@ static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0
      * loop, so the next step's CTAs are scheduled into slots as they drain and have their prologue done when
      * the last partial lands.  (Released at kernel entry instead, the next step's CTAs were parked early on an
      * uneven set of SMs: N = 4 000 went from 10.3 to 13.7 us per step; released late, 10.3 -> 9.2.) */
-    const uint32_t grid = (t1 - t0) * sim->plan.nslab;
+    const uint32_t grid = (t1 - t0) * sim->plan.ngroups;
     const bool pdl = sim->pdl;
-    sim->plan.var->launch(grid, sh.stream, p, pdl);
+    if (sim->plan.group_slabs > 1) sim->plan.var->launch_grouped(grid, sh.stream, p, pdl);
+    else sim->plan.var->launch(grid, sh.stream, p, pdl);
     NB_CUDA(cudaGetLastError());
     sim->kernels_launched++;
 }
@@ -943,6 +1034,8 @@ void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm
     out->slab_len = pl.slab_packs * 4;
     out->slabs = pl.nslab;
     out->ctas_per_sm = pl.ctas_per_sm;
+    out->group_slabs = pl.group_slabs;
+    out->groups = pl.ngroups;
     if (tile_ranges)
         for (int q = 0; q < shards; q++)
             nb::shard_tiles(pl, shards, q, &tile_ranges[4 * q], &tile_ranges[4 * q + 1], &tile_ranges[4 * q + 2],
@@ -984,6 +1077,7 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     out->threads = sim->plan.var->threads;
     out->slab_len = sim->plan.slab_packs * 4;
     out->slabs = sim->plan.nslab;
+    out->group_slabs = sim->plan.group_slabs;
     uint32_t tiles = 0;
     for (const nb::Shard &sh : sim->shards) tiles += (sh.a1 - sh.a0) + (sh.b1 - sh.b0);
     out->tiles_local = tiles;

@@ -17,10 +17,25 @@ template <int TJP, int NS>
 constexpr size_t step_smem_bytes() {
     return (size_t)NS * TJP * 48 + 2 * NS * sizeof(uint64_t) + 16;
 }
+/* GROUPED kernels keep the running sum over the slabs of their group in shared memory (one float2 per target:
+ * registers are spoken for -- 122 of 128 at 512 threads) */
+template <int THREADS, int T, int TJP, int NS>
+constexpr size_t step_smem_bytes_grouped() {
+    return step_smem_bytes<TJP, NS>() + (size_t)THREADS * T * sizeof(float2);
+}
 
-template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM = kFormPacked>
+/*
+ * GROUPED = false: one CTA = one (target tile, slab).
+ * GROUPED = true:  one CTA = one (target tile, group of consecutive slabs).  The summation order keeps its slab
+ *   structure -- even/odd chains inside a slab, slab sum = even + odd -- but the CTA adds the slab sums of its
+ *   group in slab order itself (p.fold_tiles source tiles per slab) and only the GROUP sum goes through the
+ *   partial buffer: p.nslab and p.slab_packs then count groups.  Used for Worlds whose per-slab partials would
+ *   not fit a fixed budget (sim_cuda.cu plan_host): the buffer is nslab x N x 8 B, and nslab grows with M.
+ */
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM = kFormPacked, bool GROUPED = false>
 __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_constant__ StepParams p) {
     constexpr bool TP = FORM == kFormTargetPacked;
+    static_assert(!GROUPED || FORM == kFormPacked, "slab groups exist for the packed form only");
     static_assert(!TP || T % 2 == 0, "the target-packed form needs an even number of targets per thread");
     constexpr int TR = TP ? T / 2 : T; /* f32x2 register sets per thread */
     static_assert(TJP % UNR == 0, "tile must be a multiple of the unroll");
@@ -33,6 +48,7 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
     float4 *st_gm = st_xy + (size_t)NS * TJP * 2;                         /* [NS][TJP]    */
     uint64_t *full = reinterpret_cast<uint64_t *>(st_gm + (size_t)NS * TJP);
     uint64_t *empty = full + NS;
+    float2 *run_s = reinterpret_cast<float2 *>(empty + NS); /* GROUPED: [T][THREADS] running sum over slabs */
     __shared__ int s_last;
 
     const uint32_t tid = threadIdx.x;
@@ -106,6 +122,9 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
     }
     __syncthreads(); /* barrier inits visible to every thread before the first wait */
 
+    [[maybe_unused]] uint32_t fold_left = GROUPED ? p.fold_tiles : 0u; /* GROUPED: source tiles until the current slab ends */
+    [[maybe_unused]] bool have_run = false;
+
     for (uint32_t k = 0; k < ntile; k++) {
         if (tid == 0 && k + PF < ntile) issue(k + PF);
         const uint32_t s = k % NS;
@@ -127,6 +146,25 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
         }
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
+        if constexpr (GROUPED) {
+            /* a slab of this group ends here (slabs are whole source tiles): its sum even + odd joins the
+             * running sum, in slab order, and the chains restart.  The group's last slab is folded below. */
+            if (--fold_left == 0 && k + 1 < ntile) {
+                fold_left = p.fold_tiles;
+#pragma unroll
+                for (int t = 0; t < T; t++) {
+                    float2 a = make_float2(__fadd_rn(ax[t].x, ax[t].y), __fadd_rn(ay[t].x, ay[t].y));
+                    if (have_run) {
+                        const float2 r = run_s[t * THREADS + tid];
+                        a = make_float2(__fadd_rn(r.x, a.x), __fadd_rn(r.y, a.y));
+                    }
+                    run_s[t * THREADS + tid] = a;
+                    ax[t] = make_float2(0.f, 0.f);
+                    ay[t] = make_float2(0.f, 0.f);
+                }
+                have_run = true;
+            }
+        }
     }
 
     /* pair loop done: let the next step's grid be scheduled into the slots that free up from here on */
@@ -142,6 +180,12 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
             a[2 * k + 1] = make_float2(ax[k].y, ay[k].y);
         } else {
             a[k] = make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+            if constexpr (GROUPED) {
+                if (have_run) {
+                    const float2 r = run_s[k * THREADS + tid];
+                    a[k] = make_float2(__fadd_rn(r.x, a[k].x), __fadd_rn(r.y, a[k].y));
+                }
+            }
         }
     }
 

@@ -33,6 +33,38 @@ def test_single_process_multi_gpu_bitwise_equal_to_one_gpu(nb, oracle, n, gpus):
     assert plain.tobytes() == one.tobytes()
 
 
+@pytest.mark.parametrize("gpus", [2, 8])
+def test_slab_groups_bitwise_equal_across_gpu_counts(nb, oracle, monkeypatch, gpus):
+    """The GROUPED plan (large Worlds; forced here with NBODY_PART_BUDGET) is a function of (N, M) only."""
+    if nb.device_count() < gpus:
+        pytest.skip(f"needs {gpus} GPUs")
+    n = 300000
+    arr, m = oracle.partition(nb.make_galaxies(n, 2))
+    base, _ = nb.plan(n, m, 1)
+    monkeypatch.setenv("NBODY_PART_BUDGET", str(4 * base["tiles"] * base["tile_targets"] * 8 + 8))
+    one, info1 = _run(nb, arr, m, 3, 0.01, local_gpus=1)
+    many, info = _run(nb, arr, m, 3, 0.01, local_gpus=gpus)
+    assert info1["group_slabs"] > 1 and info["group_slabs"] == info1["group_slabs"]
+    assert many.tobytes() == one.tobytes()
+
+
+def test_caller_device_is_restored(nb, oracle):
+    """Advisor finding (round 1): the entry points used to leave the CUDA current device changed."""
+    torch = pytest.importorskip("torch")
+    if nb.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    arr, m = oracle.partition(nb.make_galaxies(5000, 2))
+    torch.cuda.set_device(1)
+    x = torch.zeros(4, device="cuda")                       # context on device 1, current device 1
+    with nb.SimPipeline(len(arr), m, device=0, local_gpus=1) as sim:
+        sim.set_data(arr)
+        sim.update(2, 0.01)
+        sim.get_data()
+        assert torch._C._cuda_getDevice() == 1
+    assert torch._C._cuda_getDevice() == 1 and x.device.index == 1
+    torch.cuda.set_device(0)
+
+
 def test_world_api_with_nbody_ngpus_env(nb, oracle, monkeypatch):
     if nb.device_count() < 2:
         pytest.skip("needs 2 GPUs")

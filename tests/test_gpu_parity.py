@@ -79,6 +79,31 @@ def test_one_step_against_oracle(nb, oracle, n, gal):
     _check_one_step(nb, oracle, w0, ref1, 0.01, f"galaxy {n}/{gal}", strict=n <= 20000)
 
 
+@pytest.mark.parametrize("want_groups,n", [(1, 20000), (3, 20000), (5, 50000), (2, 4003)])
+def test_slab_groups_against_oracle(nb, oracle, monkeypatch, want_groups, n):
+    """Large Worlds (N >= 2M) run the GROUPED kernel: a CTA walks several slabs and adds their sums itself, so that the
+    partial buffer stays within a fixed budget (nslab x N x 8 B otherwise).  NBODY_PART_BUDGET forces the same plan
+    shape at sizes the oracle finishes in seconds: same parity bar as the ungrouped plan, chained == single steps."""
+    ps = nb.make_galaxies(n, 2)
+    w0, m = oracle.partition(ps)
+    base, _ = nb.plan(n, m, 1)
+    monkeypatch.setenv("NBODY_PART_BUDGET", str(want_groups * base["tiles"] * base["tile_targets"] * 8 + 8))
+    info, _ = nb.plan(n, m, 1)
+    assert info["group_slabs"] > 1 and info["groups"] <= want_groups
+    ref1 = oracle.update(w0, m, 0.01, 1, 8)
+    with nb.World(w0) as w:
+        w.update_gpu(0.01, 1)
+        pinfo = w.pipeline_info()
+    assert pinfo["group_slabs"] == info["group_slabs"] and pinfo["slabs"] == info["slabs"]
+    _check_one_step(nb, oracle, w0, ref1, 0.01, f"galaxy {n}/2, {info['slabs']} slabs in {info['groups']} group(s)",
+                    strict=n <= 20000)
+    with nb.World(ps) as a, nb.World(ps) as b:
+        a.update_gpu(0.01, 4)
+        for _ in range(4):
+            b.update_gpu(0.01, 1)
+        assert a.particles().tobytes() == b.particles().tobytes()
+
+
 @pytest.mark.parametrize("name", ["galaxy_1000_2.npz", "galaxy_4003_2.npz"])
 def test_ten_steps_against_reference_fixture(nb, golden, name):
     g = golden(name)

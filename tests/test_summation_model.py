@@ -3,6 +3,8 @@
 The plan (NbSimPlan: tile size, slab length) fixes the order in which the step kernel adds the pair terms of a target:
 inside a slab, even-numbered sources go to one FP32 accumulator and odd-numbered ones to another, in source order
 (FMA); the slab partial is their sum; slab partials are added in slab order (step_kernel.cuh, force_kernel.cuh).
+With slab groups (large Worlds, NbSimPlanInfo.group_slabs > 1) the slabs of a group are added in slab order first,
+then the group sums in group order.
 Here that order is replayed in NumPy FP32 (exact 1/sqrt instead of MUFU.RSQ, which changes single terms by ~1 ulp but
 not the growth of the rounding error with the chain length) on the reference's golden fixtures, so that a planner
 change that lengthens the chains shows up as lost accuracy on the build machine, before any GPU run.
@@ -20,11 +22,11 @@ def _fma(a, b, c):
     return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(F32)
 
 
-def replay_step_kernel_acc(w0, m, slab_len, nslab):
+def replay_step_kernel_acc(w0, m, slab_len, nslab, group_slabs=1):
     n = len(w0)
     x, y, rho = w0["px"], w0["py"], w0["radius"]
     gm = (w0["mass"][:m] * F32(10.0)).astype(F32)          # NB_G folded once per source (layout_kernels.cuh)
-    total = None
+    total, group = None, None
     for s in range(nslab):
         lo, hi = s * slab_len, min((s + 1) * slab_len, m)
         acc = [[np.zeros(n, F32), np.zeros(n, F32)], [np.zeros(n, F32), np.zeros(n, F32)]]
@@ -38,7 +40,10 @@ def replay_step_kernel_acc(w0, m, slab_len, nslab):
             acc[par][0] = _fma(f, dx, acc[par][0])
             acc[par][1] = _fma(f, dy, acc[par][1])
         part = np.stack([(acc[0][0] + acc[1][0]).astype(F32), (acc[0][1] + acc[1][1]).astype(F32)], axis=1)
-        total = part if total is None else (total + part).astype(F32)
+        group = part if group is None else (group + part).astype(F32)
+        if (s + 1) % group_slabs == 0 or s + 1 == nslab:        # the CTA's group sum goes to the partial buffer
+            total = group if total is None else (total + group).astype(F32)
+            group = None
     return total
 
 
@@ -71,3 +76,48 @@ def test_longer_chains_lose_accuracy_in_the_model(nb, oracle, golden):
     one = rel_acc_error(replay_step_kernel_acc(w0, m, m + (-m) % 16, 1), truth)
     many = rel_acc_error(replay_step_kernel_acc(w0, m, 192, -(-m // 192)), truth)
     assert np.percentile(many, 99) < np.percentile(one, 99)
+
+
+def test_slab_groups_bound_the_partial_buffer(nb, monkeypatch):
+    """Advisor finding (round 1): one partial per (slab, target) is O(N x M) bytes.  Past a fixed budget the plan
+    groups consecutive slabs per CTA; the buffer stays within the budget at every size, the chains do not get
+    longer, and the grouping is a function of (N, M) only (same for every shard count)."""
+    budget = 1 << 30
+    for n in (1 << 20, 1 << 21, 1 << 22, 1 << 24, 1 << 26, 3 << 26):
+        m = n // 2
+        info, _ = nb.plan(n, m, 1)
+        tiles_pad = info["tiles"] * info["tile_targets"]
+        assert info["groups"] == -(-info["slabs"] // info["group_slabs"])
+        assert info["groups"] * tiles_pad * 8 <= budget or info["groups"] == 1, (n, info)
+        assert info["slab_len"] <= 16384 and info["slabs"] * info["slab_len"] >= m
+        if info["group_slabs"] > 1:
+            assert info["slab_len"] % 512 == 0 or info["variant"] == "t128x2"     # whole source tiles
+        for shards in (2, 8):
+            other, _ = nb.plan(n, m, shards)
+            assert other == info
+    one_m, _ = nb.plan(1 << 20, 523884, 1)
+    assert one_m["group_slabs"] == 1 and one_m["slabs"] == 37      # the measured N = 1M plan is untouched
+    # forced at small N (what the GPU tests use)
+    base, _ = nb.plan(20000, 9956, 1)
+    per_partial = base["tiles"] * base["tile_targets"] * 8
+    for want in (1, 3, 5):
+        monkeypatch.setenv("NBODY_PART_BUDGET", str(want * per_partial + 8))
+        info, _ = nb.plan(20000, 9956, 1)
+        assert info["group_slabs"] > 1 and info["groups"] <= want, (want, info)
+        assert info["slabs"] * info["slab_len"] >= 9956 and info["slab_len"] <= base["slab_len"]
+
+
+@pytest.mark.parametrize("name", ["galaxy_4003_2.npz", "galaxy_6000_3.npz"])
+def test_grouped_summation_order_in_the_model(nb, oracle, golden, name, monkeypatch):
+    """The grouped order (slabs of a group first, then the groups) is as accurate as the ungrouped one."""
+    g = golden(name)
+    w0 = g["world0"]
+    m = mass_len_of(w0)
+    monkeypatch.setenv("NBODY_PART_BUDGET", str(len(w0) * 8 * 3))
+    info, _ = nb.plan(len(w0), m, 1)
+    assert info["group_slabs"] > 1 and info["groups"] <= 3
+    got = replay_step_kernel_acc(w0, m, info["slab_len"], info["slabs"], info["group_slabs"])
+    truth, _ = oracle.acc_f64(w0, m)
+    ref_f64 = rel_acc_error(acc_of(g["step1"]), truth)
+    cuda_f64 = rel_acc_error(got, truth)
+    assert np.percentile(cuda_f64, 99) <= max(np.percentile(ref_f64, 99), 2e-6) * 1.05

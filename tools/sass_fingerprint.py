@@ -27,11 +27,13 @@ DEFAULT_LIB = os.path.join(ROOT, "nbody_b200", "lib", "libnbody.so")
 FINGERPRINT = os.path.join(ROOT, "profiles", "kernel_fingerprint.json")
 
 # kernels of the plan's candidate table (sim_cuda.cu NB_VARIANT): THREADS, T, TJP, NS, MINB, UNR, FORM
+# ...Lb0: one CTA per slab; ...Lb1 ("g" names): the GROUPED build, a CTA walks a group of slabs (large Worlds)
 KERNELS = {
-    "t512x4": "_ZN2nb11step_kernelILi512ELi4ELi128ELi4ELi1ELi2ELi0EEEvNS_10StepParamsE",
-    "t256x4": "_ZN2nb11step_kernelILi256ELi4ELi128ELi4ELi2ELi2ELi0EEEvNS_10StepParamsE",
-    "t128x4": "_ZN2nb11step_kernelILi128ELi4ELi128ELi4ELi4ELi2ELi0EEEvNS_10StepParamsE",
-    "t128x2": "_ZN2nb11step_kernelILi128ELi2ELi64ELi4ELi6ELi2ELi0EEEvNS_10StepParamsE",
+    "t512x4": "_ZN2nb11step_kernelILi512ELi4ELi128ELi4ELi1ELi2ELi0ELb0EEEvNS_10StepParamsE",
+    "t256x4": "_ZN2nb11step_kernelILi256ELi4ELi128ELi4ELi2ELi2ELi0ELb0EEEvNS_10StepParamsE",
+    "t128x4": "_ZN2nb11step_kernelILi128ELi4ELi128ELi4ELi4ELi2ELi0ELb0EEEvNS_10StepParamsE",
+    "t128x2": "_ZN2nb11step_kernelILi128ELi2ELi64ELi4ELi6ELi2ELi0ELb0EEEvNS_10StepParamsE",
+    "g512x4": "_ZN2nb11step_kernelILi512ELi4ELi128ELi4ELi1ELi2ELi0ELb1EEEvNS_10StepParamsE",
 }
 
 

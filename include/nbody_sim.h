@@ -81,6 +81,9 @@ typedef struct NbSimConfig {
                                      /* NCCL instead of peer stores from the kernel epilogue   */
 #define NB_SIM_FLAG_NO_OVERLAP    2u /* do not overlap the position exchange with the massless  */
                                      /* targets' kernel                                         */
+#define NB_SIM_FLAG_NO_PERSIST    4u /* one launch per step even where n chained steps of a small */
+                                     /* World could run as one cooperative launch (env            */
+                                     /* NBODY_NO_PERSIST=1 does the same)                         */
 
 SimPipeline *NbSimCreate(WorldData data, const NbSimConfig *cfg);
 
@@ -125,6 +128,9 @@ typedef struct NbSimInfo {
     uint64_t pairs_per_step;   /* total_len * mass_len                      */
     uint32_t group_slabs;   /* consecutive slabs one CTA walks (1: a CTA per slab); partials per target = */
                             /* ceil(slabs / group_slabs)                                                  */
+    uint32_t persistent_ctas;     /* largest grid that may run n >= 2 chained steps as ONE cooperative launch  */
+                                  /* (grid barrier between steps); 0: every step is its own launch             */
+    uint64_t persistent_launches; /* such launches so far (they are counted in kernels_launched too)            */
 } NbSimInfo;
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);

@@ -17,6 +17,7 @@ assert PARTICLE.itemsize == 32
 UNIQUE_ID_BYTES = 128
 FLAG_NO_PEER_STORE = 1
 FLAG_NO_OVERLAP = 2
+FLAG_NO_PERSIST = 4
 
 
 class WorldData(C.Structure):  # include/nbody_sim.h (ref sim_gpu.h:8-12)
@@ -73,6 +74,8 @@ class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
         ("kernels_launched", C.c_uint64),
         ("pairs_per_step", C.c_uint64),
         ("group_slabs", C.c_uint32),
+        ("persistent_ctas", C.c_uint32),
+        ("persistent_launches", C.c_uint64),
     ]
 
     def as_dict(self):

@@ -62,7 +62,39 @@
 #define NB_ORD_LOOP 1 /* 0: per target {sources 0,1; sources 2,3}   1: sources 0,1 for all targets, then 2,3 */
 #endif
 
+/* The same knobs for the GROUPED build of the kernel (step_kernel.cuh): its loop is scheduled by ptxas on its own,
+ * so its best source order is measured on its own (tools/schedule_lottery.py --grouped). */
+#ifndef NB_ORDG_ACC
+#define NB_ORDG_ACC NB_ORD_ACC
+#endif
+#ifndef NB_ORDG_GI
+#define NB_ORDG_GI NB_ORD_GI
+#endif
+#ifndef NB_ORDG_F
+#define NB_ORDG_F NB_ORD_F
+#endif
+#ifndef NB_ORDG_SUB
+#define NB_ORDG_SUB NB_ORD_SUB
+#endif
+#ifndef NB_ORDG_LOOP
+#define NB_ORDG_LOOP NB_ORD_LOOP
+#endif
+
 namespace nb {
+
+/* a source order as one template argument: decimal digits ACC R2 GI LOOP F SUB */
+__host__ __device__ constexpr int ord_pack(int acc, int r2, int gi, int loop, int f, int sub) {
+    return ((((acc * 10 + r2) * 10 + gi) * 10 + loop) * 10 + f) * 10 + sub;
+}
+constexpr int kOrdDefault = ord_pack(NB_ORD_ACC, NB_ORD_R2, NB_ORD_GI, NB_ORD_LOOP, NB_ORD_F, NB_ORD_SUB);
+/* R2 changes the rounding, so the grouped build shares it with the default */
+constexpr int kOrdGrouped = ord_pack(NB_ORDG_ACC, NB_ORD_R2, NB_ORDG_GI, NB_ORDG_LOOP, NB_ORDG_F, NB_ORDG_SUB);
+__host__ __device__ constexpr int ord_acc(int o) { return o / 100000 % 10; }
+__host__ __device__ constexpr int ord_r2(int o) { return o / 10000 % 10; }
+__host__ __device__ constexpr int ord_gi(int o) { return o / 1000 % 10; }
+__host__ __device__ constexpr int ord_loop(int o) { return o / 100 % 10; }
+__host__ __device__ constexpr int ord_f(int o) { return o / 10 % 10; }
+__host__ __device__ constexpr int ord_sub(int o) { return o % 10; }
 
 constexpr int kPack = 4;            /* sources per pack                                  */
 constexpr int kMaxDst = 8;          /* destinations for new source positions (GPUs)      */
@@ -161,7 +193,7 @@ enum {
     kFormCluster = 8
 };
 
-template <int FORM>
+template <int FORM, int ORD = kOrdDefault>
 __device__ __forceinline__ void interact_two(const float2 x, const float2 y, const float2 g, const float2 ntx,
                                              const float2 nty, const float2 rho, float2 &ax, float2 &ay) {
     if constexpr (FORM == kFormScalar) {
@@ -178,23 +210,25 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
         ay.x = __fmaf_rn(dy0, f0, ay.x);
         ay.y = __fmaf_rn(dy1, f1, ay.y);
     } else {
-#if NB_ORD_SUB == 1
-        const float2 dy = __fadd2_rn(y, nty);
-        const float2 dx = __fadd2_rn(x, ntx);
-#elif NB_ORD_SUB == 2
-        const float2 dx = __fadd2_rn(ntx, x);
-        const float2 dy = __fadd2_rn(nty, y);
-#else
-        const float2 dx = __fadd2_rn(x, ntx);
-        const float2 dy = __fadd2_rn(y, nty);
-#endif
-#if NB_ORD_R2 == 1
-        float2 r2 = __ffma2_rn(dx, dx, rho);
-        r2 = __ffma2_rn(dy, dy, r2);
-#else
-        float2 r2 = __ffma2_rn(dy, dy, rho);
-        r2 = __ffma2_rn(dx, dx, r2);
-#endif
+        float2 dx, dy;
+        if constexpr (ord_sub(ORD) == 1) {
+            dy = __fadd2_rn(y, nty);
+            dx = __fadd2_rn(x, ntx);
+        } else if constexpr (ord_sub(ORD) == 2) {
+            dx = __fadd2_rn(ntx, x);
+            dy = __fadd2_rn(nty, y);
+        } else {
+            dx = __fadd2_rn(x, ntx);
+            dy = __fadd2_rn(y, nty);
+        }
+        float2 r2;
+        if constexpr (ord_r2(ORD) == 1) {
+            r2 = __ffma2_rn(dx, dx, rho);
+            r2 = __ffma2_rn(dy, dy, r2);
+        } else {
+            r2 = __ffma2_rn(dy, dy, rho);
+            r2 = __ffma2_rn(dx, dx, r2);
+        }
         float2 inv;
         if constexpr (FORM == kAblateMufu || FORM == kAblateBoth) {
             inv = r2;
@@ -203,16 +237,11 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
             inv.y = rsqrt_mufu(r2.y);
         }
         const float2 inv2 = __fmul2_rn(inv, inv);
-#if NB_ORD_GI == 1
-        const float2 gi = __fmul2_rn(inv, g);
-#else
-        const float2 gi = __fmul2_rn(g, inv);
-#endif
-#if NB_ORD_F == 1
-        const float2 f = __fmul2_rn(gi, inv2);
-#else
-        const float2 f = __fmul2_rn(inv2, gi);
-#endif
+        float2 gi, f;
+        if constexpr (ord_gi(ORD) == 1) gi = __fmul2_rn(inv, g);
+        else gi = __fmul2_rn(g, inv);
+        if constexpr (ord_f(ORD) == 1) f = __fmul2_rn(gi, inv2);
+        else f = __fmul2_rn(inv2, gi);
         if constexpr (FORM == kAblateAccRead || FORM == kAblateBoth) {
             /* same instruction count and dependences on dx (through r2), dy and f, but each accumulate
              * FFMA2 reads two distinct register pairs instead of three */
@@ -224,41 +253,41 @@ __device__ __forceinline__ void interact_two(const float2 x, const float2 y, con
             ay.x = __fmaf_rn(dy.x, f.x, ay.x);
             ay.y = __fmaf_rn(dy.y, f.y, ay.y);
         } else {
-#if NB_ORD_ACC == 1
-            ax = __ffma2_rn(f, dx, ax);
-            ay = __ffma2_rn(f, dy, ay);
-#elif NB_ORD_ACC == 2
-            ay = __ffma2_rn(dy, f, ay);
-            ax = __ffma2_rn(dx, f, ax);
-#else
-            ax = __ffma2_rn(dx, f, ax);
-            ay = __ffma2_rn(dy, f, ay);
-#endif
+            if constexpr (ord_acc(ORD) == 1) {
+                ax = __ffma2_rn(f, dx, ax);
+                ay = __ffma2_rn(f, dy, ay);
+            } else if constexpr (ord_acc(ORD) == 2) {
+                ay = __ffma2_rn(dy, f, ay);
+                ax = __ffma2_rn(dx, f, ax);
+            } else {
+                ax = __ffma2_rn(dx, f, ax);
+                ay = __ffma2_rn(dy, f, ay);
+            }
         }
     }
 }
 
 /* 4 sources (one pack) against T register-resident targets. */
-template <int T, int FORM = kFormPacked>
+template <int T, int FORM = kFormPacked, int ORD = kOrdDefault>
 __device__ __forceinline__ void interact_pack(const float4 xs, const float4 ys, const float4 gs,
                                               const float2 (&ntx)[T], const float2 (&nty)[T],
                                               const float2 (&rho)[T], float2 (&ax)[T], float2 (&ay)[T]) {
     const float2 x01 = make_float2(xs.x, xs.y), x23 = make_float2(xs.z, xs.w);
     const float2 y01 = make_float2(ys.x, ys.y), y23 = make_float2(ys.z, ys.w);
     const float2 g01 = make_float2(gs.x, gs.y), g23 = make_float2(gs.z, gs.w);
-#if NB_ORD_LOOP == 1
-    /* sources 0,1 against every target, then sources 2,3: per target the same order either way */
+    if constexpr (ord_loop(ORD) == 1) {
+        /* sources 0,1 against every target, then sources 2,3: per target the same order either way */
 #pragma unroll
-    for (int t = 0; t < T; t++) interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+        for (int t = 0; t < T; t++) interact_two<FORM, ORD>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
 #pragma unroll
-    for (int t = 0; t < T; t++) interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
-#else
+        for (int t = 0; t < T; t++) interact_two<FORM, ORD>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+    } else {
 #pragma unroll
-    for (int t = 0; t < T; t++) {
-        interact_two<FORM>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
-        interact_two<FORM>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+        for (int t = 0; t < T; t++) {
+            interact_two<FORM, ORD>(x01, y01, g01, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+            interact_two<FORM, ORD>(x23, y23, g23, ntx[t], nty[t], rho[t], ax[t], ay[t]);
+        }
     }
-#endif
 }
 
 /*

@@ -18,6 +18,7 @@
 #include "layout_kernels.cuh"
 #include "nbody_sim.h"
 #include "nccl_dyn.h"
+#include "persist_kernel.cuh"
 #include "render_kernels.cuh"
 #include "step_kernel.cuh"
 #include "util.cuh"
@@ -38,7 +39,25 @@ struct Variant {
     size_t smem_grouped;
     const void *func_grouped;
     void (*launch_grouped)(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl);
+    /* n chained steps in one cooperative launch (persist_kernel.cuh); null where it is not built */
+    const void *func_persist;
+    void (*launch_persist)(uint32_t grid, cudaStream_t st, const PersistParams &pp);
 };
+
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+static void launch_persistent(uint32_t grid, cudaStream_t st, const PersistParams &pp) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = step_smem_bytes<TJP, NS>();
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative; /* all CTAs co-resident, or the launch fails: they meet in a grid barrier */
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    NB_CUDA(cudaLaunchKernelEx(&cfg, step_kernel_persistent<THREADS, T, TJP, NS, MINB, UNR>, pp));
+}
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR, int FORM, bool GROUPED = false>
 static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
@@ -73,25 +92,29 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     {                                                                                                 \
         NAME, THREADS, T, TJP, NS, MINB, UNR, REL, FORM == kFormCluster, step_smem_bytes<TJP, NS>(),  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr                 \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr, nullptr, nullptr \
     }
 /* a plan candidate: also built as a GROUPED kernel for Worlds whose per-slab partials exceed the budget */
-#define NB_VARIANT_G(NAME, THREADS, T, TJP, NS, MINB, UNR, REL)                                              \
+#define NB_VARIANT_G(NAME, THREADS, T, TJP, NS, MINB, UNR, REL, PERSIST_FUNC, PERSIST_LAUNCH)                \
     {                                                                                                        \
         NAME, THREADS, T, TJP, NS, MINB, UNR, REL, false, step_smem_bytes<TJP, NS>(),                        \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked>,                          \
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked>,                                     \
             step_smem_bytes_grouped<THREADS, T, TJP, NS>(),                                                  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>,                    \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>                                \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>, PERSIST_FUNC, PERSIST_LAUNCH  \
     }
+/* the small-World candidate is also built as the persistent multi-step kernel (persist_kernel.cuh) */
+#define NB_PERSIST_FUNC(THREADS, T, TJP, NS, MINB, UNR) (const void *)step_kernel_persistent<THREADS, T, TJP, NS, MINB, UNR>
+#define NB_PERSIST_LAUNCH(THREADS, T, TJP, NS, MINB, UNR) launch_persistent<THREADS, T, TJP, NS, MINB, UNR>
 
 static const Variant kVariants[] = {
     /* plan candidates, with their measured cost per pair relative to t512x4 (profiles/r01_tune_sweep*.txt) */
-    NB_VARIANT_G("t512x4", 512, 4, 128, 4, 1, 2, 1.000), /* 2048 targets per CTA, 1 CTA/SM  */
-    NB_VARIANT_G("t256x4", 256, 4, 128, 4, 2, 2, 1.010), /* 1024 targets per CTA            */
-    NB_VARIANT_G("t128x4", 128, 4, 128, 4, 4, 2, 1.025), /* 512 targets per CTA             */
-    NB_VARIANT_G("t128x2", 128, 2, 64, 4, 6, 2, 1.065),  /* 256 targets per CTA, small N    */
+    NB_VARIANT_G("t512x4", 512, 4, 128, 4, 1, 2, 1.000, nullptr, nullptr), /* 2048 targets per CTA, 1 CTA/SM  */
+    NB_VARIANT_G("t256x4", 256, 4, 128, 4, 2, 2, 1.010, nullptr, nullptr), /* 1024 targets per CTA            */
+    NB_VARIANT_G("t128x4", 128, 4, 128, 4, 4, 2, 1.025, nullptr, nullptr), /* 512 targets per CTA             */
+    NB_VARIANT_G("t128x2", 128, 2, 64, 4, 6, 2, 1.065, NB_PERSIST_FUNC(128, 2, 64, 4, 6, 2),
+                 NB_PERSIST_LAUNCH(128, 2, 64, 4, 6, 2)), /* 256 targets per CTA, small N */
     /* selectable with NBODY_VARIANT only */
     NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked, 0.0),
     NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked, 0.0),
@@ -317,6 +340,8 @@ struct Shard { /* one GPU driven by this process */
     float2 *pos = nullptr, *vel = nullptr, *acc = nullptr, *part = nullptr;
     float *radius = nullptr;
     unsigned *tile_cnt = nullptr;
+    unsigned *grid_bar = nullptr; /* arrival counter of the persistent kernel's grid barrier */
+    unsigned bar_base = 0;        /* its value once everything enqueued so far has run          */
     double *scratch64 = nullptr;
     uint32_t a0 = 0, a1 = 0; /* massive target tiles [a0, a1)  */
     uint32_t b0 = 0, b1 = 0; /* massless target tiles [b0, b1) */
@@ -333,6 +358,8 @@ struct SimPipeline {
     int exchange = nb::kExchangeNone;
     bool overlap = true;
     bool pdl = true;          /* programmatic dependent launch between chained steps */
+    bool allow_persist = true; /* n chained steps of a small World as one cooperative launch */
+    uint32_t persist_ctas = 0; /* largest grid the persistent multi-step kernel may be launched with (0: never) */
     int cur = 0;              /* which src_xy buffer holds the current positions */
     bool has_data = false;
     bool inert = false;       /* total_len == 0: no device state, every call is a no-op (the reference's CPU
@@ -340,6 +367,7 @@ struct SimPipeline {
                                  pipeline eagerly, ref world.c:52) */
     bool timed = false;       /* ev_begin/ev_end recorded at least once          */
     uint64_t kernels_launched = 0;
+    uint64_t persistent_launches = 0; /* of those, cooperative launches of the persistent multi-step kernel */
     cudaDeviceProp prop;
     /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
     std::vector<uint32_t> all_a0, all_a1, all_b0, all_b1;
@@ -435,6 +463,16 @@ static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
     NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, plan_func(pl), pl.var->threads, plan_smem(pl)));
     NB_ASSERT(occ >= pl.var->minb, "kernel variant %s%s: %d CTAs/SM resident, %d planned", pl.var->name,
               pl.group_slabs > 1 ? " (grouped)" : "", occ, pl.var->minb);
+    /* n chained steps of a small World in one cooperative launch: only when the whole grid is co-resident */
+    sim->persist_ctas = 0;
+    if (pl.var->func_persist && pl.group_slabs == 1 && sim->total_shards == 1 && sim->allow_persist) {
+        int coop = 0, pocc = 0, dev = 0;
+        NB_CUDA(cudaGetDevice(&dev)); /* the pipeline's first device is current here */
+        NB_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+        NB_CUDA(cudaFuncSetAttribute(pl.var->func_persist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.var->smem));
+        NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pocc, pl.var->func_persist, pl.var->threads, pl.var->smem));
+        if (coop) sim->persist_ctas = (uint32_t)pocc * (uint32_t)sim->prop.multiProcessorCount;
+    }
 }
 
 }  // namespace nb
@@ -486,6 +524,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
     sim->total_shards = sim->world * sim->local_gpus;
     sim->overlap = !(cfg.flags & NB_SIM_FLAG_NO_OVERLAP) && !env_int("NBODY_NO_OVERLAP", 0);
     sim->pdl = !env_int("NBODY_NO_PDL", 0);
+    sim->allow_persist = !(cfg.flags & NB_SIM_FLAG_NO_PERSIST) && !env_int("NBODY_NO_PERSIST", 0);
 
     NB_CUDA(cudaSetDevice(first_dev));
     NB_CUDA(cudaGetDeviceProperties(&sim->prop, first_dev));
@@ -563,6 +602,8 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         /* partial sums only for the tiles this GPU computes: [nslab][own tiles * tile] */
         sh.part = dev_alloc<float2>(pl.ngroups > 1 ? (size_t)pl.ngroups * own_targets : 1);
         sh.tile_cnt = dev_alloc<unsigned>(pl.ntiles);
+        sh.grid_bar = dev_alloc<unsigned>(1);
+        NB_CUDA(cudaMemsetAsync(sh.grid_bar, 0, sizeof(unsigned), sh.stream));
         sh.scratch64 = dev_alloc<double>(8);
         /* on the stream the step kernels run on: the legacy default stream does not order with it */
         NB_CUDA(cudaMemsetAsync(sh.tile_cnt, 0, sizeof(unsigned) * pl.ntiles, sh.stream));
@@ -614,7 +655,7 @@ static void destroy_pipeline(SimPipeline *sim) {
         if (sh.comm) NB_NCCL(nccl().CommDestroy(sh.comm));
         cudaFree(sh.aos); cudaFree(sh.src_xy[0]); cudaFree(sh.src_xy[1]); cudaFree(sh.src_gm);
         cudaFree(sh.pos); cudaFree(sh.vel); cudaFree(sh.acc); cudaFree(sh.radius);
-        cudaFree(sh.part); cudaFree(sh.tile_cnt); cudaFree(sh.scratch64);
+        cudaFree(sh.part); cudaFree(sh.tile_cnt); cudaFree(sh.grid_bar); cudaFree(sh.scratch64);
         cudaEventDestroy(sh.ev_begin); cudaEventDestroy(sh.ev_end); cudaEventDestroy(sh.ev_massive);
         cudaEventDestroy(sh.ev_comm); cudaEventDestroy(sh.ev_step);
         if (sh.own_stream) cudaStreamDestroy(sh.stream);
@@ -817,8 +858,8 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
     p->dt = dt;
 }
 
-static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
-    if (t1 <= t0) return;
+/* Point P at the target tiles [t0, t1) of this GPU; returns the grid size. */
+static uint32_t aim_at_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
     p.tile_first = t0;
     /* partial slots are local: the massive tiles [a0, a1) come first, the massless tiles [b0, b1) follow.
      * The kernel indexes by global particle number, so the base pointer is biased here (never dereferenced
@@ -826,11 +867,16 @@ static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0
      * ptxas schedule of the inner loop. */
     const size_t first = (size_t)(t0 >= sh.b0 && t0 >= sh.a1 ? sh.b0 - (sh.a1 - sh.a0) : sh.a0) * sim->plan.tile;
     p.part = sh.part ? reinterpret_cast<float2 *>(reinterpret_cast<uintptr_t>(sh.part) - first * sizeof(float2)) : nullptr;
+    return (t1 - t0) * sim->plan.ngroups;
+}
+
+static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
+    if (t1 <= t0) return;
+    const uint32_t grid = aim_at_tiles(sim, sh, p, t0, t1);
     /* Programmatic dependent launch on every launch: the kernel releases its dependents after its pair
      * loop, so the next step's CTAs are scheduled into slots as they drain and have their prologue done when
      * the last partial lands.  (Released at kernel entry instead, the next step's CTAs were parked early on an
      * uneven set of SMs: N = 4 000 went from 10.3 to 13.7 us per step; released late, 10.3 -> 9.2.) */
-    const uint32_t grid = (t1 - t0) * sim->plan.ngroups;
     const bool pdl = sim->pdl;
     if (sim->plan.group_slabs > 1) sim->plan.var->launch_grouped(grid, sh.stream, p, pdl);
     else sim->plan.var->launch(grid, sh.stream, p, pdl);
@@ -865,6 +911,26 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         NB_CUDA(cudaEventRecord(sh.ev_begin, sh.stream));
     }
     const bool split = sim->exchange == kExchangeNccl && sim->overlap;
+    /* Small World, several steps: one cooperative launch of the persistent kernel runs all of them, a grid
+     * barrier between steps instead of a kernel boundary (persist_kernel.cuh).  Same plan, same bits. */
+    if (n >= 2 && L == 1 && sim->exchange == kExchangeNone && sim->persist_ctas > 0) {
+        Shard &sh = sim->shards[0];
+        PersistParams pp;
+        fill_params(sim, 0, dt, &pp.s);
+        const uint32_t grid = aim_at_tiles(sim, sh, pp.s, sh.a0, sh.b1);
+        if (sh.a1 == sh.b0 && grid > 0 && grid <= sim->persist_ctas) {
+            pp.bar = sh.grid_bar;
+            pp.bar_base = sh.bar_base;
+            pp.nsteps = n;
+            sim->plan.var->launch_persist(grid, sh.stream, pp);
+            NB_CUDA(cudaGetLastError());
+            sh.bar_base += (n - 1) * grid; /* the last step ends at the kernel boundary, not at the barrier */
+            sim->kernels_launched++;
+            sim->persistent_launches++;
+            sim->cur ^= (int)(n & 1u);
+            n = 0; /* nothing left for the launch-per-step loop */
+        }
+    }
     for (uint32_t it = 0; it < n; it++) {
         const int nxt = sim->cur ^ 1;
         for (int l = 0; l < L; l++) {
@@ -1078,6 +1144,8 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     out->slab_len = sim->plan.slab_packs * 4;
     out->slabs = sim->plan.nslab;
     out->group_slabs = sim->plan.group_slabs;
+    out->persistent_ctas = sim->persist_ctas;
+    out->persistent_launches = sim->persistent_launches;
     uint32_t tiles = 0;
     for (const nb::Shard &sh : sim->shards) tiles += (sh.a1 - sh.a0) + (sh.b1 - sh.b0);
     out->tiles_local = tiles;

@@ -122,10 +122,8 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
     }
     __syncthreads(); /* barrier inits visible to every thread before the first wait */
 
-    [[maybe_unused]] uint32_t fold_left = GROUPED ? p.fold_tiles : 0u; /* GROUPED: source tiles until the current slab ends */
-    [[maybe_unused]] bool have_run = false;
-
-    for (uint32_t k = 0; k < ntile; k++) {
+    /* One source tile against this thread's targets. */
+    auto consume_tile = [&](uint32_t k) {
         if (tid == 0 && k + PF < ntile) issue(k + PF);
         const uint32_t s = k % NS;
         mbar_wait(&full[s], (k / NS) & 1);
@@ -141,16 +139,24 @@ __global__ void __launch_bounds__(THREADS, MINB) step_kernel(const __grid_consta
                 const float4 ys = xy[2 * (q + u) + 1];
                 const float4 gs = gm[q + u];
                 if constexpr (TP) interact_pack_tp<TR>(xs, ys, gs, ntx, nty, rho, ax, ay);
-                else interact_pack<TR, FORM>(xs, ys, gs, ntx, nty, rho, ax, ay);
+                else interact_pack<TR, FORM, GROUPED ? kOrdGrouped : kOrdDefault>(xs, ys, gs, ntx, nty, rho, ax, ay);
             }
         }
         __syncwarp();
         if ((tid & 31) == 0) mbar_arrive(&empty[s]);
-        if constexpr (GROUPED) {
-            /* a slab of this group ends here (slabs are whole source tiles): its sum even + odd joins the
-             * running sum, in slab order, and the chains restart.  The group's last slab is folded below. */
-            if (--fold_left == 0 && k + 1 < ntile) {
-                fold_left = p.fold_tiles;
+    };
+
+    [[maybe_unused]] bool have_run = false;
+    if constexpr (!GROUPED) {
+        for (uint32_t k = 0; k < ntile; k++) consume_tile(k);
+    } else {
+        /* the slabs of this group, one after the other: whole source tiles each (p.fold_tiles).  A finished slab's
+         * sum even + odd joins the running sum, in slab order, and the chains restart; the group's last slab is
+         * folded below, with the epilogue. */
+        for (uint32_t k0 = 0; k0 < ntile; k0 += p.fold_tiles) {
+            const uint32_t k1 = min(k0 + p.fold_tiles, ntile);
+            for (uint32_t k = k0; k < k1; k++) consume_tile(k);
+            if (k1 < ntile) {
 #pragma unroll
                 for (int t = 0; t < T; t++) {
                     float2 a = make_float2(__fadd_rn(ax[t].x, ax[t].y), __fadd_rn(ay[t].x, ay[t].y));

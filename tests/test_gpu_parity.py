@@ -175,6 +175,41 @@ def test_chained_steps_equal_single_steps_bitwise(nb):
         assert a.particles().tobytes() == b.particles().tobytes()
 
 
+@pytest.mark.parametrize("n,steps", [(250, 2), (250, 100), (1000, 3), (2000, 17), (4003, 10), (6000, 5), (10000, 4)])
+def test_persistent_multi_step_kernel_equals_one_launch_per_step_bitwise(nb, oracle, n, steps):
+    """Small Worlds run n >= 2 chained steps as ONE cooperative launch with a grid barrier between steps
+    (persist_kernel.cuh).  Same plan, same summation order: not a bit may differ from n launches."""
+    from nbody_b200.api import FLAG_NO_PERSIST
+    arr, m = oracle.partition(nb.make_galaxies(n, 2))
+    with nb.SimPipeline(n, m) as a, nb.SimPipeline(n, m, flags=FLAG_NO_PERSIST) as b:
+        a.set_data(arr)
+        b.set_data(arr)
+        a.update(steps, 0.01)
+        b.update(steps, 0.01)
+        ia, ib = a.info(), b.info()
+        assert ia["persistent_launches"] == 1 and ia["kernels_launched"] < ib["kernels_launched"]
+        assert ib["persistent_launches"] == 0
+        assert a.get_data().tobytes() == b.get_data().tobytes()
+        # a second call continues from the right buffer (odd and even step counts) and the barrier counter carries on
+        a.update(3, 0.02)
+        b.update(3, 0.02)
+        a.update(1, 0.01)
+        b.update(1, 0.01)
+        a.update(2, 0.01)
+        b.update(2, 0.01)
+        assert a.get_data().tobytes() == b.get_data().tobytes()
+        assert a.info()["persistent_launches"] == 3
+
+
+def test_large_worlds_do_not_take_the_persistent_path(nb, oracle):
+    n = 50000
+    arr, m = oracle.partition(nb.make_galaxies(n, 2))
+    with nb.SimPipeline(n, m) as a:
+        a.set_data(arr)
+        a.update(3, 0.01)
+        assert a.info()["persistent_launches"] == 0
+
+
 def test_get_between_updates_does_not_disturb_state(nb):
     ps = nb.make_galaxies(3000, 2)
     with nb.World(ps) as a, nb.World(ps) as b:

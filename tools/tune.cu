@@ -381,6 +381,63 @@ static void run_variant(Buffers &b, uint32_t nslab_req, int sms) {
     fflush(stdout);
 }
 
+/* The GROUPED build of a plan candidate: NSLAB_REQ slabs (whole source tiles) walked by NGROUPS CTAs per tile. */
+template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
+static void run_variant_grouped(Buffers &b, uint32_t nslab_req, uint32_t ngroups_req, int sms) {
+    auto kern = step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>;
+    const size_t smem = step_smem_bytes_grouped<THREADS, T, TJP, NS>();
+    NB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 0;
+    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, THREADS, smem));
+    cudaFuncAttributes fa;
+    NB_CUDA(cudaFuncGetAttributes(&fa, kern));
+    const uint32_t tile = THREADS * T;
+    const uint32_t ntiles = (b.N + tile - 1) / tile;
+    uint32_t slab_packs = std::max<uint32_t>(TJP, ((b.src_packs + nslab_req - 1) / nslab_req) / TJP * TJP);
+    const uint32_t nslab = (b.src_packs + slab_packs - 1) / slab_packs;
+    const uint32_t gs = (nslab + ngroups_req - 1) / ngroups_req;
+    const uint32_t groups = (nslab + gs - 1) / gs;
+    StepParams p;
+    memset(&p, 0, sizeof p);
+    p.src_xy = b.src_xy[0];
+    p.src_gm = b.src_gm;
+    p.dst_xy[0] = (float *)b.src_xy[1];
+    p.ndst = 1;
+    p.pos = b.pos; p.vel = b.vel; p.acc = b.acc; p.radius = b.radius;
+    p.part = b.part; p.tile_cnt = b.cnt;
+    p.total_len = b.N; p.mass_len = b.M;
+    p.part_stride = ntiles * tile;
+    p.src_packs_pad = (b.src_packs + TJP - 1) / TJP * TJP;
+    p.slab_packs = slab_packs * gs; p.nslab = groups;
+    p.fold_tiles = slab_packs / TJP;
+    p.tile_first = 0;
+    p.dt = 0.f;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const uint32_t grid = ntiles * groups;
+    for (int w = 0; w < 2; w++) kern<<<grid, THREADS, smem>>>(p);
+    NB_CUDA(cudaDeviceSynchronize());
+    float best = 1e30f, sum = 0.f;
+    const int reps = 5;
+    for (int r = 0; r < reps; r++) {
+        cudaEventRecord(e0);
+        kern<<<grid, THREADS, smem>>>(p);
+        cudaEventRecord(e1);
+        NB_CUDA(cudaDeviceSynchronize());
+        float ms;
+        cudaEventElapsedTime(&ms, e0, e1);
+        best = std::min(best, ms);
+        sum += ms;
+    }
+    const double rate = (double)b.N * b.M / (best * 1e-3);
+    printf("  grouped t%dx%d tjp%d ns%d unr%d minb%d | regs %3d occ %d | nslab %4u in %3u groups of %3u, grid %6u waves %7.2f | "
+           "best %8.3f ms avg %8.3f | %7.1f Gpairs/s  %5.1f%% of FP32 peak (14 flop/pair)\n",
+           THREADS, T, TJP, NS, UNR, MINB, fa.numRegs, occ, nslab, groups, gs, grid, (double)grid / (occ * sms), best,
+           sum / reps, rate * 1e-9, 100.0 * rate * 14.0 / g_peak_flops);
+    fflush(stdout);
+}
+
 static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
     printf("variant sweep: N = %u targets, M = %u sources, %.3e pairs/step\n", N, M, (double)N * M);
     Buffers b = make_buffers(N, M);
@@ -400,6 +457,11 @@ static void sweep(uint32_t N, uint32_t M, int sms, const char *nslab_list) {
     for (uint32_t ns : list) {
         if (set && !strcmp(set, "ship")) { /* the large-N kernel only */
             run_variant<512, 4, 128, 4, 1, 2, 0>(b, ns, sms);
+            continue;
+        }
+        if (set && !strcmp(set, "ship-grouped")) { /* its GROUPED build: TUNE_GROUPS CTAs per tile (default 13) */
+            const char *g = getenv("TUNE_GROUPS");
+            run_variant_grouped<512, 4, 128, 4, 1, 2>(b, ns, g ? (uint32_t)atoi(g) : 13u, sms);
             continue;
         }
 #ifndef TUNE_MINIMAL

@@ -81,9 +81,10 @@ typedef struct NbSimConfig {
                                      /* NCCL instead of peer stores from the kernel epilogue   */
 #define NB_SIM_FLAG_NO_OVERLAP    2u /* do not overlap the position exchange with the massless  */
                                      /* targets' kernel                                         */
-#define NB_SIM_FLAG_NO_PERSIST    4u /* one launch per step even where n chained steps of a small */
-                                     /* World could run as one cooperative launch (env            */
-                                     /* NBODY_NO_PERSIST=1 does the same)                         */
+#define NB_SIM_FLAG_PERSIST       4u /* run n >= 2 chained steps of a small World as ONE cooperative */
+                                     /* launch with a grid barrier between steps (env NBODY_PERSIST=1  */
+                                     /* does the same).  Bit-identical to n launches and measured       */
+                                     /* slower on B200 (persist_kernel.cuh): off by default             */
 
 SimPipeline *NbSimCreate(WorldData data, const NbSimConfig *cfg);
 
@@ -128,8 +129,8 @@ typedef struct NbSimInfo {
     uint64_t pairs_per_step;   /* total_len * mass_len                      */
     uint32_t group_slabs;   /* consecutive slabs one CTA walks (1: a CTA per slab); partials per target = */
                             /* ceil(slabs / group_slabs)                                                  */
-    uint32_t persistent_ctas;     /* largest grid that may run n >= 2 chained steps as ONE cooperative launch  */
-                                  /* (grid barrier between steps); 0: every step is its own launch             */
+    uint32_t persistent_ctas;     /* NB_SIM_FLAG_PERSIST only: largest grid that runs n >= 2 chained steps as  */
+                                  /* ONE cooperative launch; 0: every step is its own launch (the default)     */
     uint64_t persistent_launches; /* such launches so far (they are counted in kernels_launched too)            */
 } NbSimInfo;
 

@@ -17,7 +17,7 @@ assert PARTICLE.itemsize == 32
 UNIQUE_ID_BYTES = 128
 FLAG_NO_PEER_STORE = 1
 FLAG_NO_OVERLAP = 2
-FLAG_NO_PERSIST = 4
+FLAG_PERSIST = 4
 
 
 class WorldData(C.Structure):  # include/nbody_sim.h (ref sim_gpu.h:8-12)

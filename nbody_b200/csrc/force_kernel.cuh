@@ -63,21 +63,23 @@
 #endif
 
 /* The same knobs for the GROUPED build of the kernel (step_kernel.cuh): its loop is scheduled by ptxas on its own,
- * so its best source order is measured on its own (tools/schedule_lottery.py --grouped). */
+ * so its best source order is measured on its own (tools/schedule_lottery.py --grouped: 24 distinct schedules,
+ * 158.7 .. 163.2 ms at N = 1M against 156.1 ms for the ungrouped kernel, profiles/r02_schedule_lottery_grouped.txt;
+ * the ungrouped kernel's own best order gives the grouped one 161.1 ms). */
 #ifndef NB_ORDG_ACC
-#define NB_ORDG_ACC NB_ORD_ACC
+#define NB_ORDG_ACC 0
 #endif
 #ifndef NB_ORDG_GI
-#define NB_ORDG_GI NB_ORD_GI
+#define NB_ORDG_GI 0
 #endif
 #ifndef NB_ORDG_F
-#define NB_ORDG_F NB_ORD_F
+#define NB_ORDG_F 1
 #endif
 #ifndef NB_ORDG_SUB
-#define NB_ORDG_SUB NB_ORD_SUB
+#define NB_ORDG_SUB 0
 #endif
 #ifndef NB_ORDG_LOOP
-#define NB_ORDG_LOOP NB_ORD_LOOP
+#define NB_ORDG_LOOP 0
 #endif
 
 namespace nb {

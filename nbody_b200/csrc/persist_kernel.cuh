@@ -23,6 +23,18 @@
  * The grid barrier is a monotonic arrival counter in global memory (one red.release per CTA, ld.acquire polling);
  * the host passes the counter's value at launch, so nothing is reset between launches.  All CTAs must be
  * co-resident: the launch is cooperative and sim_cuda.cu only takes this path when the grid fits.
+ *
+ * MEASURED ON B200 (round 2, profiles/r02_persistent_kernel.txt; nbody-bench protocol, us per step, 100 steps per
+ * call): bit-identical to n launches at every size tried -- and SLOWER than them:
+ *       N          250    1000    2000    4000    8000
+ *   persistent     5.8     8.4     8.5    11.4    19.4
+ *   n launches     3.7     6.5     6.3     8.1    18.3      (programmatic dependent launch, step_kernel.cuh)
+ * With every fence of the barrier and of the ticket removed (unsafe, timing only) it is still 5.7 / 7.7 / 7.5 /
+ * 10.5 / 17.7: on this GPU a kernel boundary with programmatic dependent launch costs LESS than one software grid
+ * barrier (a red, then ld.acquire polling across 148 SMs, then every CTA's first L2 round trips all over again --
+ * which the dependent launch overlaps with the previous step's tail).  So this kernel is NOT the default: it runs
+ * only with NBODY_PERSIST=1 / NB_SIM_FLAG_PERSIST, and is kept as the record of that measurement plus its parity
+ * test (tests/test_gpu_parity.py).
  */
 #pragma once
 

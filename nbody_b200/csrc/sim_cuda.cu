@@ -221,7 +221,7 @@ static double weighted_cost(const Plan &pl, uint32_t N, int sm_count, uint32_t n
 /* Bytes the slab partials of ONE GPU running the whole World may take (nslab x targets x 8 B).  A constant, not
  * the free memory of the device at hand: the plan fixes the summation order and must be a function of (N, M)
  * only.  NBODY_PART_BUDGET (bytes) overrides it -- for tests, which force slab groups at small N with it. */
-static const uint64_t kPartBudgetBytes = 1ull << 30;
+static const uint64_t kPartBudgetBytes = 8ull << 30; /* N <= 4M (4.3 GB) keeps one CTA per slab, as measured */
 static uint64_t part_budget_bytes() {
     const char *e = getenv("NBODY_PART_BUDGET");
     if (e && *e) return std::max<uint64_t>(1, strtoull(e, nullptr, 10));
@@ -231,7 +231,9 @@ static uint64_t part_budget_bytes() {
 /*
  * Slab groups: bound the partial buffer.  The slab count grows with M (no accumulator chain longer than
  * kMaxSlabSources / 2 terms), so one partial per (slab, target) is nslab x N x 8 B = O(N x M): 310 MB at N = 1M,
- * 4.3 GB at 4M, 69 GB at 16M.  Past the budget a CTA walks `group_slabs` consecutive slabs and adds their sums in
+ * 4.3 GB at 4M, 69 GB at 16M.  Past the budget (the GROUPED build's pair loop is 1.7 % slower than the ungrouped
+ * one even with its own best source order -- profiles/r02_schedule_lottery_grouped.txt -- so it is not used where
+ * the plain buffer is affordable) a CTA walks `group_slabs` consecutive slabs and adds their sums in
  * slab order itself (step_kernel GROUPED); only ngroups = ceil(nslab / group_slabs) partials per target reach
  * memory.  Slabs become whole source tiles for this; the number of groups is chosen by the same timing model as
  * the slab count.  Returns the model cost of the final plan.
@@ -358,7 +360,8 @@ struct SimPipeline {
     int exchange = nb::kExchangeNone;
     bool overlap = true;
     bool pdl = true;          /* programmatic dependent launch between chained steps */
-    bool allow_persist = true; /* n chained steps of a small World as one cooperative launch */
+    bool allow_persist = false; /* n chained steps of a small World as one cooperative launch: opt-in, measured
+                                   slower than n launches with programmatic dependent launch (persist_kernel.cuh) */
     uint32_t persist_ctas = 0; /* largest grid the persistent multi-step kernel may be launched with (0: never) */
     int cur = 0;              /* which src_xy buffer holds the current positions */
     bool has_data = false;
@@ -463,7 +466,7 @@ static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
     NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, plan_func(pl), pl.var->threads, plan_smem(pl)));
     NB_ASSERT(occ >= pl.var->minb, "kernel variant %s%s: %d CTAs/SM resident, %d planned", pl.var->name,
               pl.group_slabs > 1 ? " (grouped)" : "", occ, pl.var->minb);
-    /* n chained steps of a small World in one cooperative launch: only when the whole grid is co-resident */
+    /* opt-in: n chained steps of a small World in one cooperative launch, only when the whole grid is co-resident */
     sim->persist_ctas = 0;
     if (pl.var->func_persist && pl.group_slabs == 1 && sim->total_shards == 1 && sim->allow_persist) {
         int coop = 0, pocc = 0, dev = 0;
@@ -524,7 +527,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
     sim->total_shards = sim->world * sim->local_gpus;
     sim->overlap = !(cfg.flags & NB_SIM_FLAG_NO_OVERLAP) && !env_int("NBODY_NO_OVERLAP", 0);
     sim->pdl = !env_int("NBODY_NO_PDL", 0);
-    sim->allow_persist = !(cfg.flags & NB_SIM_FLAG_NO_PERSIST) && !env_int("NBODY_NO_PERSIST", 0);
+    sim->allow_persist = (cfg.flags & NB_SIM_FLAG_PERSIST) || env_int("NBODY_PERSIST", 0);
 
     NB_CUDA(cudaSetDevice(first_dev));
     NB_CUDA(cudaGetDeviceProperties(&sim->prop, first_dev));
@@ -911,8 +914,9 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         NB_CUDA(cudaEventRecord(sh.ev_begin, sh.stream));
     }
     const bool split = sim->exchange == kExchangeNccl && sim->overlap;
-    /* Small World, several steps: one cooperative launch of the persistent kernel runs all of them, a grid
-     * barrier between steps instead of a kernel boundary (persist_kernel.cuh).  Same plan, same bits. */
+    /* Opt-in (NBODY_PERSIST=1): small World, several steps: one cooperative launch of the persistent kernel runs all
+     * of them, a grid barrier between steps instead of a kernel boundary (persist_kernel.cuh).  Same plan, same
+     * bits -- and measured slower than the launches below, which is why it is not the default. */
     if (n >= 2 && L == 1 && sim->exchange == kExchangeNone && sim->persist_ctas > 0) {
         Shard &sh = sim->shards[0];
         PersistParams pp;

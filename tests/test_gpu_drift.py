@@ -78,6 +78,27 @@ def test_thousand_step_drift_matches_reference(nb, oracle, golden, name):
     assert np.median(d) <= 1e-4 * scale
 
 
+@pytest.mark.parametrize("name,meets", [("drift_6000_3.npz", True), ("drift_16384_2.npz", False)])
+def test_literal_drift_bound_one_percent(nb, oracle, golden, request, name, meets):
+    """north_star's drift criterion as worded: energy drift over 1,000 steps within 1 % of the reference's.  At
+    N = 16384 the reference's own AVX / SSE / scalar builds differ by 11.6 % in that drift (it is 3e-5 of |E| and
+    follows the rounding order of a few close encounters); the CUDA path lands 10-30 % away depending on its plan.
+    Recorded as a strict xfail: a miss of the literal criterion, reported as a miss."""
+    if not meets:
+        request.applymarker(pytest.mark.xfail(strict=True, reason="literal 1 % drift bound missed at N = 16384 "
+                                                                  "(reference's own builds: 11.6 % apart)"))
+    g = golden(name)
+    n, gal, dt, m = int(g["n"]), int(g["galaxies"]), float(g["dt"]), int(g["mass_len"])
+    with nb.World(nb.make_galaxies(n, gal, seed=int(g["seed"]))) as w:
+        e_start = oracle.diagnostics(w.particles(), m)["E"]
+        w.update_gpu(dt, 1000)
+        e_end = oracle.diagnostics(w.particles(), m)["E"]
+    de_ref = g["diag"][-1, 5] - g["diag"][0, 5]
+    de_got = e_end - e_start
+    print(f"\n[literal drift] {name}: ref {de_ref:.4e} cuda {de_got:.4e} ratio {de_got / de_ref:.4f}")
+    assert abs(de_got - de_ref) <= 0.01 * abs(de_ref)
+
+
 def test_device_diagnostics_match_oracle(nb, oracle):
     ps = nb.make_galaxies(6000, 3)
     arr, m = oracle.partition(ps)

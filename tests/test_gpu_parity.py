@@ -79,6 +79,37 @@ def test_one_step_against_oracle(nb, oracle, n, gal):
     _check_one_step(nb, oracle, w0, ref1, 0.01, f"galaxy {n}/{gal}", strict=n <= 20000)
 
 
+# The tolerance exactly as north_star words it -- EVERY particle's acceleration within 1e-5 of the reference's after one
+# step -- with the measured worst particle on B200 (round 2).  Where the reference's own FP32 rounding noise against FP64
+# is already above the bound (third column) no implementation with another summation order can meet it: those
+# cases are strict xfails, so the miss stays visible and a change that closes it is noticed.
+LITERAL_CASES = [
+    # n, galaxies, worst cuda-vs-ref, worst ref-vs-f64, meets the literal bound
+    (1000, 2, 9.9e-07, 8.7e-07, True),
+    (4003, 2, 2.4e-06, 2.8e-06, True),
+    (6000, 3, 3.6e-05, 5.1e-05, False),
+    (16384, 2, 8.1e-06, 1.0e-05, True),
+    (20000, 2, 1.3e-05, 1.5e-05, False),
+    (50000, 2, 6.7e-05, 8.0e-05, False),
+]
+
+
+@pytest.mark.parametrize("n,gal,worst,ref_noise,meets", LITERAL_CASES)
+def test_literal_north_star_bound_on_every_particle(nb, oracle, request, n, gal, worst, ref_noise, meets):
+    if not meets:
+        request.applymarker(pytest.mark.xfail(strict=True, reason=(
+            f"literal bound missed: worst particle {worst:.1e} vs the reference (the reference itself is {ref_noise:.1e} "
+            "from FP64 on its worst particle)")))
+    w0, m = oracle.partition(nb.make_galaxies(n, gal))
+    ref1 = oracle.update(w0, m, 0.01, 1, 8)
+    with nb.World(w0) as w:
+        w.update_gpu(0.01, 1)
+        got = w.particles()
+    err = rel_acc_error(acc_of(got), acc_of(ref1))
+    print(f"\n[literal] N={n}/{gal}: worst particle {err.max():.2e} (recorded {worst:.1e}), p99 {np.percentile(err, 99):.2e}")
+    assert err.max() <= TOL_ACC
+
+
 @pytest.mark.parametrize("want_groups,n", [(1, 20000), (3, 20000), (5, 50000), (2, 4003)])
 def test_slab_groups_against_oracle(nb, oracle, monkeypatch, want_groups, n):
     """Large Worlds (N >= 2M) run the GROUPED kernel: a CTA walks several slabs and adds their sums itself, so that the
@@ -177,11 +208,12 @@ def test_chained_steps_equal_single_steps_bitwise(nb):
 
 @pytest.mark.parametrize("n,steps", [(250, 2), (250, 100), (1000, 3), (2000, 17), (4003, 10), (6000, 5), (10000, 4)])
 def test_persistent_multi_step_kernel_equals_one_launch_per_step_bitwise(nb, oracle, n, steps):
-    """Small Worlds run n >= 2 chained steps as ONE cooperative launch with a grid barrier between steps
-    (persist_kernel.cuh).  Same plan, same summation order: not a bit may differ from n launches."""
-    from nbody_b200.api import FLAG_NO_PERSIST
+    """Opt-in path (NB_SIM_FLAG_PERSIST): n >= 2 chained steps of a small World as ONE cooperative launch with a grid
+    barrier between steps (persist_kernel.cuh; measured slower than n launches, hence not the default).  Same plan,
+    same summation order: not a bit may differ from n launches."""
+    from nbody_b200.api import FLAG_PERSIST
     arr, m = oracle.partition(nb.make_galaxies(n, 2))
-    with nb.SimPipeline(n, m) as a, nb.SimPipeline(n, m, flags=FLAG_NO_PERSIST) as b:
+    with nb.SimPipeline(n, m, flags=FLAG_PERSIST) as a, nb.SimPipeline(n, m) as b:
         a.set_data(arr)
         b.set_data(arr)
         a.update(steps, 0.01)
@@ -202,9 +234,10 @@ def test_persistent_multi_step_kernel_equals_one_launch_per_step_bitwise(nb, ora
 
 
 def test_large_worlds_do_not_take_the_persistent_path(nb, oracle):
+    from nbody_b200.api import FLAG_PERSIST
     n = 50000
     arr, m = oracle.partition(nb.make_galaxies(n, 2))
-    with nb.SimPipeline(n, m) as a:
+    with nb.SimPipeline(n, m, flags=FLAG_PERSIST) as a:
         a.set_data(arr)
         a.update(3, 0.01)
         assert a.info()["persistent_launches"] == 0

@@ -349,7 +349,7 @@ def run_ours(args):
         "bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
         "traffic": traffic,
         "peak_source": "derived: SMs x 128 x 2 x max SM clock (MEASURED_PEAKS.json has no FP32 figure)",
-        "kernel": f"nb::step_kernel ({info['threads']} threads x {info['tile_targets'] // info['threads']} targets, "
+        "kernel": f"nb::step_kernel {info['variant']} ({info['threads']} threads, {info['tile_targets']} targets per CTA, "
                   f"{info['slabs']} slabs of {info['slab_len']} sources)",
         "flop_per_pair": FLOP_PER_PAIR,
         "ceiling_frac": 14.0 / 18.0,

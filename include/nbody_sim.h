@@ -132,6 +132,7 @@ typedef struct NbSimInfo {
     uint32_t persistent_ctas;     /* NB_SIM_FLAG_PERSIST only: largest grid that runs n >= 2 chained steps as  */
                                   /* ONE cooperative launch; 0: every step is its own launch (the default)     */
     uint64_t persistent_launches; /* such launches so far (they are counted in kernels_launched too)            */
+    char variant[16];             /* kernel variant of the plan (NbSimPlanInfo.variant)                         */
 } NbSimInfo;
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);

@@ -76,6 +76,7 @@ class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
         ("group_slabs", C.c_uint32),
         ("persistent_ctas", C.c_uint32),
         ("persistent_launches", C.c_uint64),
+        ("variant", C.c_char * 16),
     ]
 
     def as_dict(self):

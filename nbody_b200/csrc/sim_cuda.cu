@@ -20,6 +20,7 @@
 #include "nccl_dyn.h"
 #include "persist_kernel.cuh"
 #include "render_kernels.cuh"
+#include "small_kernel.cuh"
 #include "step_kernel.cuh"
 #include "util.cuh"
 
@@ -42,7 +43,29 @@ struct Variant {
     /* n chained steps in one cooperative launch (persist_kernel.cuh); null where it is not built */
     const void *func_persist;
     void (*launch_persist)(uint32_t grid, cudaStream_t st, const PersistParams &pp);
+    /* small-World kernel (small_kernel.cuh): a tile is 32 * T targets, its slabs are split over the warps of ONE
+     * CTA, all sources sit in shared memory (sized per World at launch) */
+    bool small;
 };
+
+template <int WARPS, int T, int UNR>
+static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(WARPS * 32);
+    cfg.dynamicSmemBytes = small_smem_bytes(p.src_packs_pad, p.nslab, T);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    unsigned na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    NB_CUDA(cudaLaunchKernelEx(&cfg, small_world_kernel<WARPS, T, UNR>, p));
+}
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
 static void launch_persistent(uint32_t grid, cudaStream_t st, const PersistParams &pp) {
@@ -92,7 +115,7 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     {                                                                                                 \
         NAME, THREADS, T, TJP, NS, MINB, UNR, REL, FORM == kFormCluster, step_smem_bytes<TJP, NS>(),  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr, nullptr, nullptr \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr, nullptr, nullptr, false \
     }
 /* a plan candidate: also built as a GROUPED kernel for Worlds whose per-slab partials exceed the budget */
 #define NB_VARIANT_G(NAME, THREADS, T, TJP, NS, MINB, UNR, REL, PERSIST_FUNC, PERSIST_LAUNCH)                \
@@ -102,7 +125,14 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked>,                                     \
             step_smem_bytes_grouped<THREADS, T, TJP, NS>(),                                                  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>,                    \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>, PERSIST_FUNC, PERSIST_LAUNCH  \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>, PERSIST_FUNC, PERSIST_LAUNCH, \
+            false                                                                                            \
+    }
+/* the small-World kernel: WARPS warps per CTA, T targets per lane; TJP only rounds the source padding */
+#define NB_VARIANT_SMALL(NAME, WARPS, T, UNR)                                                                \
+    {                                                                                                        \
+        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)small_world_kernel<WARPS, T, UNR>,  \
+            launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true                         \
     }
 /* the small-World candidate is also built as the persistent multi-step kernel (persist_kernel.cuh) */
 #define NB_PERSIST_FUNC(THREADS, T, TJP, NS, MINB, UNR) (const void *)step_kernel_persistent<THREADS, T, TJP, NS, MINB, UNR>
@@ -119,6 +149,14 @@ static const Variant kVariants[] = {
     NB_VARIANT("t256x2", 256, 2, 128, 4, 3, 2, kFormPacked, 0.0),
     NB_VARIANT("t128x8", 128, 8, 128, 4, 2, 1, kFormPacked, 0.0),
     NB_VARIANT("t64x4", 64, 4, 64, 4, 8, 2, kFormPacked, 0.0),
+    /* small Worlds: slabs split over the warps of one CTA, sources resident in shared memory (small_kernel.cuh);
+     * chosen by small_variant_for, or with NBODY_VARIANT */
+    NB_VARIANT_SMALL("w32x1", 32, 1, 2), /* planned: N <= 32 SMs         */
+    NB_VARIANT_SMALL("w16x2", 16, 2, 2), /* planned: N <= 64 SMs         */
+    NB_VARIANT_SMALL("w16x3", 16, 3, 2), /* planned: 0.78 x 96 SMs <= N <= 96 SMs   */
+    NB_VARIANT_SMALL("w16x4", 16, 4, 2), /* planned: 0.78 x 128 SMs <= N <= 128 SMs */
+    NB_VARIANT_SMALL("w16x1", 16, 1, 2), /* NBODY_VARIANT only (the sweep's other candidates) */
+    NB_VARIANT_SMALL("w8x1", 8, 1, 2),
     /* slab reduction through distributed shared memory: bit-identical, measured slower (cluster_reduce.cuh) */
     NB_VARIANT("c128x2", 128, 2, 64, 4, 6, 2, kFormCluster, 0.0),
     NB_VARIANT("c128x4", 128, 4, 128, 4, 4, 2, kFormCluster, 0.0),
@@ -193,7 +231,7 @@ static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uin
 static void set_geometry(Plan &pl, const Variant *v, uint32_t N, uint32_t M) {
     pl.var = v;
     pl.ctas_per_sm = v->minb;
-    pl.tile = (uint32_t)v->threads * v->T;
+    pl.tile = v->small ? 32u * (uint32_t)v->T : (uint32_t)v->threads * v->T;
     pl.ntiles = ceil_div(N, pl.tile);
     pl.mtiles = ceil_div(M, pl.tile);
     pl.n_pad = pl.ntiles * pl.tile;
@@ -313,16 +351,69 @@ static double choose_slabs_ungrouped(Plan &pl, uint32_t N, int sm_count, uint32_
     return best;
 }
 
+/* Slabs of a small World (small_kernel.cuh): the warps of the tile's one CTA share them out, so equal lengths,
+ * one per warp -- or k per warp once a slab would exceed 512 sources (chains of 256 terms).  The slab sums never
+ * leave shared memory: no partial buffer, no groups. */
+static void choose_slabs_small(Plan &pl, uint32_t forced_slab_len) {
+    const uint32_t unr = 4;
+    const uint32_t warps = (uint32_t)pl.var->threads / 32;
+    pl.group_slabs = 1;
+    pl.ngroups = 1;
+    if (pl.src_packs == 0) {
+        pl.slab_packs = unr;
+        pl.nslab = 1;
+        return;
+    }
+    if (forced_slab_len) {
+        pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
+    } else {
+        const uint32_t per_warp = ceil_div(pl.src_packs, warps * 128u);
+        pl.slab_packs = std::max(unr, ceil_div(ceil_div(pl.src_packs, warps * per_warp), unr) * unr);
+    }
+    pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
+}
+
 static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
+    if (pl.var->small) {
+        choose_slabs_small(pl, forced_slab_len);
+        return 0.0;
+    }
     const double cost = choose_slabs_ungrouped(pl, N, sm_count, forced_slab_len);
     return group_slabs(pl, N, sm_count, cost);
+}
+
+static const Variant *find_variant(const char *name) {
+    for (int i = 0; i < kNumVariants; i++)
+        if (strcmp(name, kVariants[i].name) == 0) return &kVariants[i];
+    return nullptr;
+}
+
+/*
+ * Which Worlds take the small-World kernel (small_kernel.cuh), and with how many targets per lane.  One CTA per
+ * tile of 32 * T targets and no more CTAs than SMs (a second CTA on an SM doubles that SM's work: measured cliff),
+ * so T = ceil(N / (32 * SMs)), up to 4.  Measured against the (tile, slab)-per-CTA kernel on B200
+ * (profiles/r02_small_world_variants.txt, us per step): N = 1 000 3.6 vs 6.9; 4 000 5.7 vs 8.1; 4 736 6.4 vs 10.6;
+ * 8 000 14.3 vs 18.4; 9 472 16.4 vs 23.2 (T <= 2: always faster); T = 3 and 4 win only when most SMs get a CTA
+ * (12 000 28.6 vs 30.9, 14 208 32.8 vs 39.2, 18 944 56.2 vs 63.3, but 10 000 24.3 vs 22.5 and 15 000 a tie), hence
+ * the utilisation floor.  Best warp count per T from the same sweep: 32 warps at T = 1, 16 above.
+ * NBODY_SMALL_MAX_N caps N (0: never use the small-World kernel).
+ */
+static const size_t kSmallWorldMaxSmem = 200u << 10;
+static const double kSmallWorldMinUtil = 0.78; /* T >= 3: CTAs / SMs */
+static const Variant *small_variant_for(uint32_t N, int sm_count) {
+    const char *e = getenv("NBODY_SMALL_MAX_N");
+    if (e && *e && N > (uint32_t)strtoul(e, nullptr, 10)) return nullptr;
+    const uint32_t T = ceil_div(N, 32u * (uint32_t)sm_count);
+    if (T == 0 || T > 4) return nullptr;
+    if (T >= 3 && (double)ceil_div(N, 32u * T) < kSmallWorldMinUtil * sm_count) return nullptr;
+    const char *name = T == 1 ? "w32x1" : T == 2 ? "w16x2" : T == 3 ? "w16x3" : "w16x4";
+    return find_variant(name);
 }
 
 static const Variant *forced_variant() {
     const char *e = getenv("NBODY_VARIANT");
     if (!e || !*e) return nullptr;
-    for (int i = 0; i < kNumVariants; i++)
-        if (strcmp(e, kVariants[i].name) == 0) return &kVariants[i];
+    if (const Variant *v = find_variant(e)) return v;
     NB_FAIL("NBODY_VARIANT=%s is not a known kernel variant", e);
 }
 
@@ -419,7 +510,19 @@ static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab
     if (const Variant *v = forced_variant()) {
         set_geometry(pl, v, N, M);
         choose_slabs(pl, N, sm_count, forced_slab);
+        if (v->small)
+            NB_ASSERT(small_smem_bytes(pl.src_packs_pad, pl.nslab, v->T) <= kSmallWorldMaxSmem,
+                      "NBODY_VARIANT=%s keeps all %u sources in shared memory: too many", v->name, M);
         return;
+    }
+    if (const Variant *v = small_variant_for(N, sm_count)) {
+        Plan cand{};
+        set_geometry(cand, v, N, M);
+        choose_slabs(cand, N, sm_count, forced_slab);
+        if (small_smem_bytes(cand.src_packs_pad, cand.nslab, v->T) <= kSmallWorldMaxSmem) {
+            pl = cand;
+            return;
+        }
     }
     double best = 1e300;
     Plan best_plan{};
@@ -452,12 +555,21 @@ static void shard_tiles(const Plan &pl, int S, int q, uint32_t *a0, uint32_t *a1
 
 /* the kernel a plan runs: the variant itself, or its GROUPED build when a CTA walks several slabs */
 static const void *plan_func(const Plan &pl) { return pl.group_slabs > 1 ? pl.var->func_grouped : pl.var->func; }
-static size_t plan_smem(const Plan &pl) { return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem; }
+/* what the function is ALLOWED to be launched with: a per-function attribute shared by every pipeline of the process,
+ * so for the small-World kernel (shared memory sized per World) it is the cap, not this World's need */
+static size_t plan_smem_limit(const Plan &pl) {
+    if (pl.var->small) return kSmallWorldMaxSmem;
+    return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem;
+}
+static size_t plan_smem(const Plan &pl) {
+    if (pl.var->small) return small_smem_bytes(pl.src_packs_pad, pl.nslab, pl.var->T);
+    return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem;
+}
 
 static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
     Plan &pl = sim->plan;
     plan_host(sim->data.total_len, sim->data.mass_len, sim->prop.multiProcessorCount, forced_slab, pl);
-    NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem(pl)));
+    NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem_limit(pl)));
     if (pl.var->cluster) {
         NB_ASSERT(pl.nslab <= kMaxClusterSlabs, "cluster variant %s with %u slabs", pl.var->name, pl.nslab);
         if (pl.nslab > 8) NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -565,7 +677,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
         sh.b0 = sim->all_b0[sh.global_index]; sh.b1 = sim->all_b1[sh.global_index];
         NB_CUDA(cudaSetDevice(sh.device));
         if (l > 0) {
-            NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem(pl)));
+            NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem_limit(pl)));
             if (pl.var->cluster && pl.nslab > 8)
                 NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         }
@@ -856,7 +968,8 @@ static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p) {
     p->part_stride = ((sh.a1 - sh.a0) + (sh.b1 - sh.b0)) * pl.tile;
     p->src_packs_pad = pl.src_packs_pad;
     /* the kernel's "slab" is what one CTA walks: a slab, or a group of slabs it folds itself (GROUPED) */
-    p->slab_packs = pl.slab_packs * pl.group_slabs; p->nslab = pl.ngroups;
+    p->slab_packs = pl.slab_packs * pl.group_slabs;
+    p->nslab = pl.var->small ? pl.nslab : pl.ngroups; /* small Worlds: all slabs inside the tile's one CTA */
     p->fold_tiles = pl.group_slabs > 1 ? pl.slab_packs / (uint32_t)pl.var->tjp : 0;
     p->dt = dt;
 }
@@ -1105,7 +1218,7 @@ void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm
     out->slabs = pl.nslab;
     out->ctas_per_sm = pl.ctas_per_sm;
     out->group_slabs = pl.group_slabs;
-    out->groups = pl.ngroups;
+    out->groups = pl.var->small ? pl.nslab : pl.ngroups; /* small Worlds: one sum per slab, in shared memory */
     if (tile_ranges)
         for (int q = 0; q < shards; q++)
             nb::shard_tiles(pl, shards, q, &tile_ranges[4 * q], &tile_ranges[4 * q + 1], &tile_ranges[4 * q + 2],
@@ -1150,6 +1263,7 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     out->group_slabs = sim->plan.group_slabs;
     out->persistent_ctas = sim->persist_ctas;
     out->persistent_launches = sim->persistent_launches;
+    strncpy(out->variant, sim->plan.var->name, sizeof out->variant - 1);
     uint32_t tiles = 0;
     for (const nb::Shard &sh : sim->shards) tiles += (sh.a1 - sh.a0) + (sh.b1 - sh.b0);
     out->tiles_local = tiles;

@@ -82,7 +82,7 @@ def test_thousand_step_drift_matches_reference(nb, oracle, golden, name):
 def test_literal_drift_bound_one_percent(nb, oracle, golden, request, name, meets):
     """north_star's drift criterion as worded: energy drift over 1,000 steps within 1 % of the reference's.  At
     N = 16384 the reference's own AVX / SSE / scalar builds differ by 11.6 % in that drift (it is 3e-5 of |E| and
-    follows the rounding order of a few close encounters); the CUDA path lands 10-30 % away depending on its plan.
+    follows the rounding order of a few close encounters); the CUDA path lands 6-30 % away depending on its plan.
     Recorded as a strict xfail: a miss of the literal criterion, reported as a miss."""
     if not meets:
         request.applymarker(pytest.mark.xfail(strict=True, reason="literal 1 % drift bound missed at N = 16384 "

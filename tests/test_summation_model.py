@@ -115,6 +115,7 @@ def test_grouped_summation_order_in_the_model(nb, oracle, golden, name, monkeypa
     w0 = g["world0"]
     m = mass_len_of(w0)
     monkeypatch.setenv("NBODY_PART_BUDGET", str(len(w0) * 8 * 3))
+    monkeypatch.setenv("NBODY_SMALL_MAX_N", "0")     # not the small-World kernel: it has no partial buffer to bound
     info, _ = nb.plan(len(w0), m, 1)
     assert info["group_slabs"] > 1 and info["groups"] <= 3
     got = replay_step_kernel_acc(w0, m, info["slab_len"], info["slabs"], info["group_slabs"])
@@ -122,3 +123,28 @@ def test_grouped_summation_order_in_the_model(nb, oracle, golden, name, monkeypa
     ref_f64 = rel_acc_error(acc_of(g["step1"]), truth)
     cuda_f64 = rel_acc_error(got, truth)
     assert np.percentile(cuda_f64, 99) <= max(np.percentile(ref_f64, 99), 2e-6) * 1.05
+
+
+def test_small_worlds_split_their_slabs_over_the_warps_of_one_cta(nb, monkeypatch):
+    """Worlds of at most 4 x 32 x 148 targets take the small-World kernel (small_kernel.cuh): one CTA per tile of
+    32 T targets, T = ceil(N / (32 x 148)), at most one CTA per SM; T = 3, 4 only when most SMs get a CTA.  Slabs
+    of equal length, at most 512 sources, one (or k) per warp; the order of summation is still 'slabs in slab order'
+    (group_slabs == 1) and does not depend on the shard count."""
+    want = {1: "w32x1", 250: "w32x1", 1000: "w32x1", 4003: "w32x1", 4736: "w32x1", 4737: "w16x2", 6000: "w16x2",
+            9472: "w16x2", 9473: "t128x2", 10000: "t128x2", 12000: "w16x3", 14208: "w16x3", 14209: "t128x2",
+            16384: "w16x4", 18944: "w16x4", 18945: "t128x2"}
+    for n, variant in want.items():
+        m = max(1, n // 2)
+        info, _ = nb.plan(n, m, 1)
+        assert info["variant"] == variant, (n, info)
+        if not variant.startswith("w"):
+            continue
+        t = int(variant[-1])
+        warps = int(variant[1:-2])
+        assert info["tile_targets"] == 32 * t and info["tiles"] <= 148 and info["group_slabs"] == 1
+        assert info["slabs"] * info["slab_len"] >= m and (info["slabs"] - 1) * info["slab_len"] < m
+        assert info["slab_len"] <= 512 and info["slab_len"] % 16 == 0
+        assert info["slabs"] <= warps * -(-m // (warps * 512))
+        assert nb.plan(n, m, 2)[0] == info
+    monkeypatch.setenv("NBODY_SMALL_MAX_N", "0")
+    assert nb.plan(1000, 485, 1)[0]["variant"] == "t128x2"

@@ -46,7 +46,7 @@ def row(tag, n, steps_per_call, calls, warm_calls, dt=1.0, galaxies=2):
         "us_per_step_wall": wall_med / steps_per_call * 1e6, "us_per_step_device": dev_med / steps_per_call * 1e6,
         "gpairs_per_s_wall": pairs / wall_med * 1e-9, "gpairs_per_s_device": pairs / dev_med * 1e-9,
         "frac_fp32_peak_device": pairs / dev_med * 14 / peak,
-        "variant": f"{info['threads']}x{info['tile_targets'] // info['threads']}", "slabs": info["slabs"],
+        "variant": info["variant"], "slabs": info["slabs"],
         "slab_len": info["slab_len"],
     }
     print(json.dumps(out), flush=True)

@@ -81,6 +81,8 @@ typedef struct NbSimConfig {
                                      /* NCCL instead of peer stores from the kernel epilogue   */
 #define NB_SIM_FLAG_NO_OVERLAP    2u /* do not overlap the position exchange with the massless  */
                                      /* targets' kernel                                         */
+#define NB_SIM_FLAG_NO_GRAPH      8u /* never replay chained steps of a small World as CUDA-graph    */
+                                     /* chunks (env NBODY_NO_GRAPH=1 does the same)                   */
 #define NB_SIM_FLAG_PERSIST       4u /* run n >= 2 chained steps of a small World as ONE cooperative */
                                      /* launch with a grid barrier between steps (env NBODY_PERSIST=1  */
                                      /* does the same).  Bit-identical to n launches and measured       */
@@ -133,6 +135,8 @@ typedef struct NbSimInfo {
                                   /* ONE cooperative launch; 0: every step is its own launch (the default)     */
     uint64_t persistent_launches; /* such launches so far (they are counted in kernels_launched too)            */
     char variant[16];             /* kernel variant of the plan (NbSimPlanInfo.variant)                         */
+    uint64_t graph_launches;      /* cudaGraphLaunch calls so far: chained steps of small Worlds are replayed   */
+    uint32_t graph_steps;         /* as CUDA-graph chunks of this many steps (0: this World never uses graphs)  */
 } NbSimInfo;
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);

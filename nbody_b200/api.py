@@ -18,6 +18,7 @@ UNIQUE_ID_BYTES = 128
 FLAG_NO_PEER_STORE = 1
 FLAG_NO_OVERLAP = 2
 FLAG_PERSIST = 4
+FLAG_NO_GRAPH = 8
 
 
 class WorldData(C.Structure):  # include/nbody_sim.h (ref sim_gpu.h:8-12)
@@ -77,6 +78,8 @@ class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
         ("persistent_ctas", C.c_uint32),
         ("persistent_launches", C.c_uint64),
         ("variant", C.c_char * 16),
+        ("graph_launches", C.c_uint64),
+        ("graph_steps", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -16,6 +16,9 @@
  *
  * The World API has no parameter for the GPU count, so --ngpus travels through env NBODY_NGPUS.
  * Pair count per step = total_len * mass_len (massless particles are targets, never sources).
+ * GB/s = algorithmic HBM bytes of a step (56 B per particle: pos, vel, radius read, pos, vel, acc written, the new
+ * source position; 12 B per source read once) over the step time -- the number that matters at small N, where the
+ * step is latency-bound and neither roofline is near.
  */
 #include <stdbool.h>
 #include <stdint.h>
@@ -98,7 +101,7 @@ int main(int argc, char **argv) {
     if (!json) {
         printf("\t      N\t      M");
         if (run_cpu) printf("\t CPU us\tCPU Gp/s");
-        if (run_gpu) printf("\t GPU us\tGPU Gp/s\t%%FP32");
+        if (run_gpu) printf("\t GPU us\tGPU Gp/s\t%%FP32\t  GB/s");
         printf("\n");
     }
     for (uint32_t k = 0; k < nsizes; k++) {
@@ -127,17 +130,20 @@ int main(int argc, char **argv) {
         }
         free(ps);
         const double pairs = (double)n * (double)m;
+        const double step_bytes = 56.0 * (double)n + 12.0 * (double)m;
         if (json) {
             printf("{\"n\": %u, \"mass_len\": %u, \"steps\": %u, \"warmup\": %u", n, m, steps, warmup);
             if (run_cpu) printf(", \"cpu_us_per_step\": %.3f, \"cpu_gpairs_per_s\": %.3f", cpu_s * 1e6, pairs / cpu_s * 1e-9);
             if (run_gpu)
-                printf(", \"gpu_us_per_step\": %.3f, \"gpu_gpairs_per_s\": %.3f, \"gpus\": %d, \"frac_fp32_peak\": %.4f",
-                       gpu_s * 1e6, pairs / gpu_s * 1e-9, gpus, frac);
+                printf(", \"gpu_us_per_step\": %.3f, \"gpu_gpairs_per_s\": %.3f, \"gpus\": %d, \"frac_fp32_peak\": %.4f, "
+                       "\"algorithmic_gbytes_per_s\": %.2f",
+                       gpu_s * 1e6, pairs / gpu_s * 1e-9, gpus, frac, step_bytes / gpu_s * 1e-9);
             printf("}\n");
         } else {
             printf("\t%7u\t%7u", n, m);
             if (run_cpu) printf("\t%7.0f\t%8.2f", cpu_s * 1e6, pairs / cpu_s * 1e-9);
-            if (run_gpu) printf("\t%7.1f\t%8.1f\t%5.1f", gpu_s * 1e6, pairs / gpu_s * 1e-9, 100.0 * frac);
+            if (run_gpu)
+                printf("\t%7.1f\t%8.1f\t%5.1f\t%6.1f", gpu_s * 1e6, pairs / gpu_s * 1e-9, 100.0 * frac, step_bytes / gpu_s * 1e-9);
             printf("\n");
         }
         fflush(stdout);

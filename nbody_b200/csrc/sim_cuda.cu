@@ -443,6 +443,18 @@ struct Shard { /* one GPU driven by this process */
 
 }  // namespace nb
 
+namespace nb {
+static const uint32_t kGraphSteps = 20;        /* steps per CUDA-graph chunk (even)                          */
+static const uint32_t kGraphMaxTargets = 4736; /* Worlds up to this size replay chained steps as graph chunks */
+}  // namespace nb
+
+/* A chunk of kGraphSteps chained steps of a small World as one instantiated CUDA graph (step_async): valid for one
+ * dt and for the source buffer the chunk starts from (the launches' arguments are baked into the graph). */
+struct StepGraph {
+    cudaGraphExec_t exec = nullptr;
+    float dt = 0.f;
+};
+
 struct SimPipeline {
     WorldData data;
     nb::Plan plan;
@@ -454,6 +466,8 @@ struct SimPipeline {
     bool allow_persist = false; /* n chained steps of a small World as one cooperative launch: opt-in, measured
                                    slower than n launches with programmatic dependent launch (persist_kernel.cuh) */
     uint32_t persist_ctas = 0; /* largest grid the persistent multi-step kernel may be launched with (0: never) */
+    bool use_graph = false;    /* chained steps of this World are host-launch-bound: run them as CUDA-graph chunks */
+    StepGraph graphs[2];       /* one per source buffer a chunk may start from */
     int cur = 0;              /* which src_xy buffer holds the current positions */
     bool has_data = false;
     bool inert = false;       /* total_len == 0: no device state, every call is a no-op (the reference's CPU
@@ -462,6 +476,7 @@ struct SimPipeline {
     bool timed = false;       /* ev_begin/ev_end recorded at least once          */
     uint64_t kernels_launched = 0;
     uint64_t persistent_launches = 0; /* of those, cooperative launches of the persistent multi-step kernel */
+    uint64_t graph_launches = 0;      /* cudaGraphLaunch calls (each replays kGraphSteps step kernels) */
     cudaDeviceProp prop;
     /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
     std::vector<uint32_t> all_a0, all_a1, all_b0, all_b1;
@@ -640,6 +655,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
     sim->overlap = !(cfg.flags & NB_SIM_FLAG_NO_OVERLAP) && !env_int("NBODY_NO_OVERLAP", 0);
     sim->pdl = !env_int("NBODY_NO_PDL", 0);
     sim->allow_persist = (cfg.flags & NB_SIM_FLAG_PERSIST) || env_int("NBODY_PERSIST", 0);
+    sim->use_graph = !(cfg.flags & NB_SIM_FLAG_NO_GRAPH) && !env_int("NBODY_NO_GRAPH", 0);
 
     NB_CUDA(cudaSetDevice(first_dev));
     NB_CUDA(cudaGetDeviceProperties(&sim->prop, first_dev));
@@ -754,6 +770,10 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
             NB_NCCL(api.GroupEnd());
         }
     }
+    /* CUDA-graph chunks only where a step is shorter than a launch takes the host (~3.5 us): the one-CTA-per-tile
+     * small-World plans on one GPU, on a stream we own (a caller's stream may itself be under capture) */
+    sim->use_graph = sim->use_graph && sim->total_shards == 1 && pl.var->small && pl.ntiles <= (uint32_t)sim->prop.multiProcessorCount &&
+                     sim->shards[0].own_stream && sim->data.total_len <= kGraphMaxTargets;
     for (Shard &sh : sim->shards) { /* creation-time initialisation done before anything else uses the buffers */
         NB_CUDA(cudaSetDevice(sh.device));
         NB_CUDA(cudaStreamSynchronize(sh.stream));
@@ -763,6 +783,8 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
 
 static void destroy_pipeline(SimPipeline *sim) {
     if (!sim) return;
+    for (StepGraph &g : sim->graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
     for (Shard &sh : sim->shards) {
         NB_CUDA(cudaSetDevice(sh.device));
         NB_CUDA(cudaStreamSynchronize(sh.stream));
@@ -1019,6 +1041,44 @@ static void exchange_nccl(SimPipeline *sim, int nxt, bool on_comm_stream) {
     NB_NCCL(api.GroupEnd());
 }
 
+/*
+ * Chained steps of a small World as CUDA-graph chunks.  With the small-World kernel a step at N <= ~1 500 takes the
+ * GPU less time than one cudaLaunchKernelEx takes the host (tools/launch_bound_probe.py: 3.5 us per launch in a
+ * 100-step call, device time 3.5 us per step = launch-bound).  A chunk of kGraphSteps launches -- the same kernels,
+ * arguments and programmatic-dependent-launch edges as the stream path, captured once per (dt, starting buffer) --
+ * is replayed with one cudaGraphLaunch; an even chunk length brings the ping-pong buffers back to where they
+ * started, so the same graph serves every chunk of a call.  The first chained call (n >= 2) prepares the graph.
+ */
+static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1);
+static void fill_params(SimPipeline *sim, int l, float dt, StepParams *p);
+
+static cudaGraphExec_t step_graph(SimPipeline *sim, float dt) {
+    StepGraph &g = sim->graphs[sim->cur];
+    if (g.exec && g.dt == dt) return g.exec;
+    if (g.exec) {
+        NB_CUDA(cudaGraphExecDestroy(g.exec));
+        g.exec = nullptr;
+    }
+    Shard &sh = sim->shards[0];
+    const int cur0 = sim->cur;
+    const uint64_t launched0 = sim->kernels_launched;
+    NB_CUDA(cudaStreamBeginCapture(sh.stream, cudaStreamCaptureModeThreadLocal));
+    for (uint32_t k = 0; k < kGraphSteps; k++) {
+        StepParams p;
+        fill_params(sim, 0, dt, &p);
+        launch_tiles(sim, sh, p, sh.a0, sh.b1);
+        sim->cur ^= 1;
+    }
+    cudaGraph_t graph = nullptr;
+    NB_CUDA(cudaStreamEndCapture(sh.stream, &graph));
+    sim->cur = cur0;
+    sim->kernels_launched = launched0; /* recorded, not launched */
+    NB_CUDA(cudaGraphInstantiate(&g.exec, graph, 0));
+    NB_CUDA(cudaGraphDestroy(graph));
+    g.dt = dt;
+    return g.exec;
+}
+
 static void step_async(SimPipeline *sim, uint32_t n, float dt) {
     NB_ASSERT(sim->has_data, "PerformSimUpdate before SetSimulationData (ref sim_gpu.h:34)");
     const int L = sim->local_gpus;
@@ -1027,6 +1087,17 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         NB_CUDA(cudaEventRecord(sh.ev_begin, sh.stream));
     }
     const bool split = sim->exchange == kExchangeNccl && sim->overlap;
+    if (sim->use_graph && n >= 2 && sim->shards[0].a1 == sim->shards[0].b0) {
+        static_assert(kGraphSteps % 2 == 0, "a chunk must bring the ping-pong buffers back");
+        Shard &sh = sim->shards[0];
+        cudaGraphExec_t exec = step_graph(sim, dt);
+        while (n >= kGraphSteps) {
+            NB_CUDA(cudaGraphLaunch(exec, sh.stream));
+            sim->kernels_launched += kGraphSteps;
+            sim->graph_launches++;
+            n -= kGraphSteps;
+        }
+    }
     /* Opt-in (NBODY_PERSIST=1): small World, several steps: one cooperative launch of the persistent kernel runs all
      * of them, a grid barrier between steps instead of a kernel boundary (persist_kernel.cuh).  Same plan, same
      * bits -- and measured slower than the launches below, which is why it is not the default. */
@@ -1264,6 +1335,8 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     out->persistent_ctas = sim->persist_ctas;
     out->persistent_launches = sim->persistent_launches;
     strncpy(out->variant, sim->plan.var->name, sizeof out->variant - 1);
+    out->graph_launches = sim->graph_launches;
+    out->graph_steps = sim->use_graph ? nb::kGraphSteps : 0;
     uint32_t tiles = 0;
     for (const nb::Shard &sh : sim->shards) tiles += (sh.a1 - sh.a0) + (sh.b1 - sh.b0);
     out->tiles_local = tiles;

@@ -284,6 +284,26 @@ def _cloud(n):
     return ps
 
 
+@pytest.mark.parametrize("n", [250, 1000, 4003])
+def test_cuda_graph_chunks_equal_stream_launches_bitwise(nb, oracle, n):
+    """Chained steps of a small World are replayed as CUDA-graph chunks of 20 steps (step_async); the remainder
+    and Worlds above 4 736 targets go launch by launch.  Same kernels, same arguments: same bits -- across odd
+    step counts (the chunk must start from either source buffer) and a change of dt (the graph is re-captured)."""
+    from nbody_b200.api import FLAG_NO_GRAPH
+    arr, m = oracle.partition(nb.make_galaxies(n, 2))
+    with nb.SimPipeline(n, m) as a, nb.SimPipeline(n, m, flags=FLAG_NO_GRAPH) as b:
+        a.set_data(arr)
+        b.set_data(arr)
+        for steps, dt in ((45, 0.01), (1, 0.01), (61, 0.01), (40, 0.02), (3, 0.02), (20, 0.01)):
+            a.update(steps, dt)
+            b.update(steps, dt)
+            assert a.get_data().tobytes() == b.get_data().tobytes(), (steps, dt)
+        ia, ib = a.info(), b.info()
+    assert ia["graph_steps"] == 20 and ib["graph_steps"] == 0
+    assert ia["graph_launches"] == 2 + 3 + 2 + 1 and ib["graph_launches"] == 0
+    assert ia["kernels_launched"] == ib["kernels_launched"]        # replayed kernels are counted like launched ones
+
+
 def test_get_between_updates_does_not_disturb_state(nb):
     ps = nb.make_galaxies(3000, 2)
     with nb.World(ps) as a, nb.World(ps) as b:

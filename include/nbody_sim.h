@@ -83,6 +83,11 @@ typedef struct NbSimConfig {
                                      /* targets' kernel                                         */
 #define NB_SIM_FLAG_NO_GRAPH      8u /* never replay chained steps of a small World as CUDA-graph    */
                                      /* chunks (env NBODY_NO_GRAPH=1 does the same)                   */
+#define NB_SIM_FLAG_EXACT        16u /* verification mode: reproduce the reference's AVX CPU update    */
+                                     /* BIT FOR BIT (IEEE sqrt and division, its 8-lane summation      */
+                                     /* order; exact_kernel.cuh) at about a quarter of the fast        */
+                                     /* kernels' rate.  env NBODY_EXACT=avx|sse|scalar does the same   */
+                                     /* for the reference's three SIMD builds                          */
 #define NB_SIM_FLAG_PERSIST       4u /* run n >= 2 chained steps of a small World as ONE cooperative */
                                      /* launch with a grid barrier between steps (env NBODY_PERSIST=1  */
                                      /* does the same).  Bit-identical to n launches and measured       */

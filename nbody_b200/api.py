@@ -19,6 +19,7 @@ FLAG_NO_PEER_STORE = 1
 FLAG_NO_OVERLAP = 2
 FLAG_PERSIST = 4
 FLAG_NO_GRAPH = 8
+FLAG_EXACT = 16
 
 
 class WorldData(C.Structure):  # include/nbody_sim.h (ref sim_gpu.h:8-12)

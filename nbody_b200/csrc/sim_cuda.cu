@@ -15,6 +15,7 @@
 #include <cstring>
 #include <vector>
 
+#include "exact_kernel.cuh"
 #include "layout_kernels.cuh"
 #include "nbody_sim.h"
 #include "nccl_dyn.h"
@@ -46,7 +47,28 @@ struct Variant {
     /* small-World kernel (small_kernel.cuh): a tile is 32 * T targets, its slabs are split over the warps of ONE
      * CTA, all sources sit in shared memory (sized per World at launch) */
     bool small;
+    /* the reference's CPU arithmetic reproduced bit for bit (exact_kernel.cuh): one thread per target, no slabs */
+    bool exact;
 };
+
+template <int LANES>
+static void launch_exact(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kExactThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    unsigned na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    NB_CUDA(cudaLaunchKernelEx(&cfg, exact_kernel<LANES>, p));
+}
 
 template <int WARPS, int T, int UNR>
 static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
@@ -115,7 +137,8 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
     {                                                                                                 \
         NAME, THREADS, T, TJP, NS, MINB, UNR, REL, FORM == kFormCluster, step_smem_bytes<TJP, NS>(),  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
-            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr, nullptr, nullptr, false \
+            launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr, nullptr, nullptr, false, \
+            false                                                                                            \
     }
 /* a plan candidate: also built as a GROUPED kernel for Worlds whose per-slab partials exceed the budget */
 #define NB_VARIANT_G(NAME, THREADS, T, TJP, NS, MINB, UNR, REL, PERSIST_FUNC, PERSIST_LAUNCH)                \
@@ -126,13 +149,19 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
             step_smem_bytes_grouped<THREADS, T, TJP, NS>(),                                                  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>,                    \
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>, PERSIST_FUNC, PERSIST_LAUNCH, \
-            false                                                                                            \
+            false, false                                                                                     \
     }
 /* the small-World kernel: WARPS warps per CTA, T targets per lane; TJP only rounds the source padding */
 #define NB_VARIANT_SMALL(NAME, WARPS, T, UNR)                                                                \
     {                                                                                                        \
         NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)small_world_kernel<WARPS, T, UNR>,  \
-            launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true                         \
+            launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true, false                  \
+    }
+/* the reference-exact verification kernel for the reference build with LANES SIMD lanes */
+#define NB_VARIANT_EXACT(NAME, LANES)                                                                        \
+    {                                                                                                        \
+        NAME, kExactThreads, 1, 64, 0, 1, 1, 0.0, false, 0, (const void *)exact_kernel<LANES>,               \
+            launch_exact<LANES>, 0, nullptr, nullptr, nullptr, nullptr, false, true                          \
     }
 /* the small-World candidate is also built as the persistent multi-step kernel (persist_kernel.cuh) */
 #define NB_PERSIST_FUNC(THREADS, T, TJP, NS, MINB, UNR) (const void *)step_kernel_persistent<THREADS, T, TJP, NS, MINB, UNR>
@@ -157,6 +186,11 @@ static const Variant kVariants[] = {
     NB_VARIANT_SMALL("w16x4", 16, 4, 2), /* planned: 0.78 x 128 SMs <= N <= 128 SMs */
     NB_VARIANT_SMALL("w16x1", 16, 1, 2), /* NBODY_VARIANT only (the sweep's other candidates) */
     NB_VARIANT_SMALL("w8x1", 8, 1, 2),
+    /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
+     * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
+    NB_VARIANT_EXACT("ref8", 8),
+    NB_VARIANT_EXACT("ref4", 4),
+    NB_VARIANT_EXACT("ref1", 1),
     /* slab reduction through distributed shared memory: bit-identical, measured slower (cluster_reduce.cuh) */
     NB_VARIANT("c128x2", 128, 2, 64, 4, 6, 2, kFormCluster, 0.0),
     NB_VARIANT("c128x4", 128, 4, 128, 4, 4, 2, kFormCluster, 0.0),
@@ -374,6 +408,13 @@ static void choose_slabs_small(Plan &pl, uint32_t forced_slab_len) {
 }
 
 static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
+    if (pl.var->exact) { /* the reference's order: LANES chains over all sources, no slabs */
+        pl.slab_packs = std::max(4u, pl.src_packs_pad);
+        pl.nslab = 1;
+        pl.group_slabs = 1;
+        pl.ngroups = 1;
+        return 0.0;
+    }
     if (pl.var->small) {
         choose_slabs_small(pl, forced_slab_len);
         return 0.0;
@@ -411,6 +452,12 @@ static const Variant *small_variant_for(uint32_t N, int sm_count) {
 }
 
 static const Variant *forced_variant() {
+    if (const char *x = getenv("NBODY_EXACT")) { /* reference-exact verification mode, by SIMD build of the reference */
+        if (!strcmp(x, "avx") || !strcmp(x, "8") || !strcmp(x, "1") || !strcmp(x, "on")) return find_variant("ref8");
+        if (!strcmp(x, "sse") || !strcmp(x, "4")) return find_variant("ref4");
+        if (!strcmp(x, "scalar")) return find_variant("ref1");
+        if (*x && strcmp(x, "0") && strcmp(x, "off")) NB_FAIL("NBODY_EXACT=%s: expected avx, sse or scalar", x);
+    }
     const char *e = getenv("NBODY_VARIANT");
     if (!e || !*e) return nullptr;
     if (const Variant *v = find_variant(e)) return v;
@@ -521,8 +568,9 @@ static Tp *dev_alloc(size_t count) {
 
 /* Geometry from sizes alone -- no device is touched, so the same plan can be computed (and
  * tested) on a machine without a GPU.  Occupancy is the variant's __launch_bounds__ promise. */
-static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl) {
-    if (const Variant *v = forced_variant()) {
+static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl,
+                      const Variant *force = nullptr) {
+    if (const Variant *v = force ? force : forced_variant()) {
         set_geometry(pl, v, N, M);
         choose_slabs(pl, N, sm_count, forced_slab);
         if (v->small)
@@ -581,9 +629,10 @@ static size_t plan_smem(const Plan &pl) {
     return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem;
 }
 
-static void make_plan(SimPipeline *sim, uint32_t forced_slab) {
+static void make_plan(SimPipeline *sim, uint32_t forced_slab, bool exact) {
     Plan &pl = sim->plan;
-    plan_host(sim->data.total_len, sim->data.mass_len, sim->prop.multiProcessorCount, forced_slab, pl);
+    plan_host(sim->data.total_len, sim->data.mass_len, sim->prop.multiProcessorCount, forced_slab, pl,
+              exact ? find_variant("ref8") : nullptr);
     NB_CUDA(cudaFuncSetAttribute(plan_func(pl), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan_smem_limit(pl)));
     if (pl.var->cluster) {
         NB_ASSERT(pl.nslab <= kMaxClusterSlabs, "cluster variant %s with %u slabs", pl.var->name, pl.nslab);
@@ -661,7 +710,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
     NB_CUDA(cudaGetDeviceProperties(&sim->prop, first_dev));
     NB_ASSERT(sim->prop.major >= 10, "device %d (%s) is sm_%d%d; this library is built for sm_100a only", first_dev,
               sim->prop.name, sim->prop.major, sim->prop.minor);
-    make_plan(sim, cfg.slab_len ? cfg.slab_len : (uint32_t)env_int("NBODY_SLAB", 0));
+    make_plan(sim, cfg.slab_len ? cfg.slab_len : (uint32_t)env_int("NBODY_SLAB", 0), (cfg.flags & NB_SIM_FLAG_EXACT) != 0);
     const Plan &pl = sim->plan;
 
     /* who computes which tiles */

@@ -15,6 +15,7 @@
 #include <cstring>
 #include <vector>
 
+#include "balanced_kernel.cuh"
 #include "exact_kernel.cuh"
 #include "layout_kernels.cuh"
 #include "nbody_sim.h"
@@ -49,6 +50,8 @@ struct Variant {
     bool small;
     /* the reference's CPU arithmetic reproduced bit for bit (exact_kernel.cuh): one thread per target, no slabs */
     bool exact;
+    /* mid-size Worlds (balanced_kernel.cuh): rows of 32 * T targets x slabs, shared out evenly over one CTA per SM */
+    bool balanced;
 };
 
 template <int LANES>
@@ -87,6 +90,26 @@ static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bo
     cfg.attrs = attr;
     cfg.numAttrs = na;
     NB_CUDA(cudaLaunchKernelEx(&cfg, small_world_kernel<WARPS, T, UNR>, p));
+}
+
+/* GRID CTAs (at most one per SM) share out p.fold_tiles rows x p.nslab slabs */
+template <int WARPS, int T, int UNR>
+static void launch_balanced(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(WARPS * 32);
+    cfg.dynamicSmemBytes = balanced_smem_bytes(p.src_packs_pad, p.nslab, T, p.fold_tiles, grid);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    unsigned na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    NB_CUDA(cudaLaunchKernelEx(&cfg, balanced_kernel<WARPS, T, UNR>, p));
 }
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
@@ -138,7 +161,7 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
         NAME, THREADS, T, TJP, NS, MINB, UNR, REL, FORM == kFormCluster, step_smem_bytes<TJP, NS>(),  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, FORM>,                          \
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, FORM>, 0, nullptr, nullptr, nullptr, nullptr, false, \
-            false                                                                                            \
+            false, false                                                                                     \
     }
 /* a plan candidate: also built as a GROUPED kernel for Worlds whose per-slab partials exceed the budget */
 #define NB_VARIANT_G(NAME, THREADS, T, TJP, NS, MINB, UNR, REL, PERSIST_FUNC, PERSIST_LAUNCH)                \
@@ -149,19 +172,25 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
             step_smem_bytes_grouped<THREADS, T, TJP, NS>(),                                                  \
             (const void *)step_kernel<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>,                    \
             launch_variant<THREADS, T, TJP, NS, MINB, UNR, kFormPacked, true>, PERSIST_FUNC, PERSIST_LAUNCH, \
-            false, false                                                                                     \
+            false, false, false                                                                              \
     }
 /* the small-World kernel: WARPS warps per CTA, T targets per lane; TJP only rounds the source padding */
 #define NB_VARIANT_SMALL(NAME, WARPS, T, UNR)                                                                \
     {                                                                                                        \
         NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)small_world_kernel<WARPS, T, UNR>,  \
-            launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true, false                  \
+            launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true, false, false           \
+    }
+/* the balanced kernel of mid-size Worlds: WARPS warps per CTA, T targets per lane, one CTA per SM */
+#define NB_VARIANT_BALANCED(NAME, WARPS, T, UNR)                                                             \
+    {                                                                                                        \
+        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)balanced_kernel<WARPS, T, UNR>,     \
+            launch_balanced<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, false, false, true        \
     }
 /* the reference-exact verification kernel for the reference build with LANES SIMD lanes */
 #define NB_VARIANT_EXACT(NAME, LANES)                                                                        \
     {                                                                                                        \
         NAME, kExactThreads, 1, 64, 0, 1, 1, 0.0, false, 0, (const void *)exact_kernel<LANES>,               \
-            launch_exact<LANES>, 0, nullptr, nullptr, nullptr, nullptr, false, true                          \
+            launch_exact<LANES>, 0, nullptr, nullptr, nullptr, nullptr, false, true, false                   \
     }
 /* the small-World candidate is also built as the persistent multi-step kernel (persist_kernel.cuh) */
 #define NB_PERSIST_FUNC(THREADS, T, TJP, NS, MINB, UNR) (const void *)step_kernel_persistent<THREADS, T, TJP, NS, MINB, UNR>
@@ -186,6 +215,13 @@ static const Variant kVariants[] = {
     NB_VARIANT_SMALL("w16x4", 16, 4, 2), /* planned: 0.78 x 128 SMs <= N <= 128 SMs */
     NB_VARIANT_SMALL("w16x1", 16, 1, 2), /* NBODY_VARIANT only (the sweep's other candidates) */
     NB_VARIANT_SMALL("w8x1", 8, 1, 2),
+    /* mid-size Worlds: (row, slab) units shared out evenly over one CTA per SM (balanced_kernel.cuh) */
+    NB_VARIANT_BALANCED("b16x2", 16, 2, 2),
+    NB_VARIANT_BALANCED("b16x1", 16, 1, 2),
+    NB_VARIANT_BALANCED("b32x1", 32, 1, 2),
+    NB_VARIANT_BALANCED("b16x4", 16, 4, 2),
+    NB_VARIANT_BALANCED("b8x4", 8, 4, 2),
+    NB_VARIANT_BALANCED("b32x2", 32, 2, 2),
     /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
      * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
     NB_VARIANT_EXACT("ref8", 8),
@@ -265,7 +301,7 @@ static double model_clocks(const Variant &v, uint32_t tiles, uint32_t nslab, uin
 static void set_geometry(Plan &pl, const Variant *v, uint32_t N, uint32_t M) {
     pl.var = v;
     pl.ctas_per_sm = v->minb;
-    pl.tile = v->small ? 32u * (uint32_t)v->T : (uint32_t)v->threads * v->T;
+    pl.tile = (v->small || v->balanced) ? 32u * (uint32_t)v->T : (uint32_t)v->threads * v->T;
     pl.ntiles = ceil_div(N, pl.tile);
     pl.mtiles = ceil_div(M, pl.tile);
     pl.n_pad = pl.ntiles * pl.tile;
@@ -407,6 +443,47 @@ static void choose_slabs_small(Plan &pl, uint32_t forced_slab_len) {
     pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
 }
 
+/* Slabs of a mid-size World (balanced_kernel.cuh): every CTA gets ceil(rows * nslab / CTAs) units at most and its
+ * warps walk them in rounds, so the slab count decides how full the last round is.  Slabs of 128 ... 512 sources
+ * (chains of 64 ... 256 terms); cost of a plan = rounds x (slab length + a fixed cost per unit). */
+static const double kBalancedUnitFixedPacks = 3.0; /* per unit, in packs of work: target fetch, index arithmetic, sum store */
+static void choose_slabs_balanced(Plan &pl, int sm_count, uint32_t forced_slab_len) {
+    const uint32_t unr = 4;
+    const uint32_t warps = (uint32_t)pl.var->threads / 32;
+    pl.group_slabs = 1;
+    if (pl.src_packs == 0) {
+        pl.slab_packs = unr;
+        pl.nslab = pl.ngroups = 1;
+        return;
+    }
+    if (forced_slab_len) {
+        pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
+    } else {
+        double best = 1e300;
+        uint32_t best_sp = 32;
+        const uint32_t n_lo = std::max(1u, ceil_div(pl.src_packs, 128u)), n_hi = std::max(n_lo, pl.src_packs / 32u);
+        for (uint32_t n = n_lo; n <= n_hi; n++) {
+            const uint32_t sp = ceil_div(ceil_div(pl.src_packs, n), unr) * unr;
+            if (ceil_div(pl.src_packs, sp) != n) continue;
+            const uint32_t units = pl.ntiles * n, ctas = std::min<uint32_t>((uint32_t)sm_count, units);
+            const uint32_t rounds = ceil_div(ceil_div(units, ctas), warps);
+            const double cost = rounds * ((double)sp + kBalancedUnitFixedPacks);
+            if (cost < best * 0.999) {
+                best = cost;
+                best_sp = sp;
+            }
+        }
+        pl.slab_packs = best_sp;
+    }
+    pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
+    pl.ngroups = pl.nslab; /* one partial per (slab, target) in memory, for the rows that straddle two CTAs */
+}
+
+static size_t balanced_plan_smem(const Plan &pl, int sm_count) {
+    const uint32_t units = pl.ntiles * pl.nslab;
+    return balanced_smem_bytes(pl.src_packs_pad, pl.nslab, pl.var->T, pl.ntiles, std::min<uint32_t>((uint32_t)sm_count, units));
+}
+
 static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_slab_len) {
     if (pl.var->exact) { /* the reference's order: LANES chains over all sources, no slabs */
         pl.slab_packs = std::max(4u, pl.src_packs_pad);
@@ -417,6 +494,10 @@ static double choose_slabs(Plan &pl, uint32_t N, int sm_count, uint32_t forced_s
     }
     if (pl.var->small) {
         choose_slabs_small(pl, forced_slab_len);
+        return 0.0;
+    }
+    if (pl.var->balanced) {
+        choose_slabs_balanced(pl, sm_count, forced_slab_len);
         return 0.0;
     }
     const double cost = choose_slabs_ungrouped(pl, N, sm_count, forced_slab_len);
@@ -440,6 +521,7 @@ static const Variant *find_variant(const char *name) {
  * NBODY_SMALL_MAX_N caps N (0: never use the small-World kernel).
  */
 static const size_t kSmallWorldMaxSmem = 200u << 10;
+static const size_t kBalancedMaxSmem = 220u << 10;
 static const double kSmallWorldMinUtil = 0.78; /* T >= 3: CTAs / SMs */
 static const Variant *small_variant_for(uint32_t N, int sm_count) {
     const char *e = getenv("NBODY_SMALL_MAX_N");
@@ -576,6 +658,9 @@ static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab
         if (v->small)
             NB_ASSERT(small_smem_bytes(pl.src_packs_pad, pl.nslab, v->T) <= kSmallWorldMaxSmem,
                       "NBODY_VARIANT=%s keeps all %u sources in shared memory: too many", v->name, M);
+        if (v->balanced)
+            NB_ASSERT(balanced_plan_smem(pl, sm_count) <= kBalancedMaxSmem,
+                      "NBODY_VARIANT=%s keeps all %u sources in shared memory: too many", v->name, M);
         return;
     }
     if (const Variant *v = small_variant_for(N, sm_count)) {
@@ -622,10 +707,12 @@ static const void *plan_func(const Plan &pl) { return pl.group_slabs > 1 ? pl.va
  * so for the small-World kernel (shared memory sized per World) it is the cap, not this World's need */
 static size_t plan_smem_limit(const Plan &pl) {
     if (pl.var->small) return kSmallWorldMaxSmem;
+    if (pl.var->balanced) return kBalancedMaxSmem;
     return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem;
 }
-static size_t plan_smem(const Plan &pl) {
+static size_t plan_smem(const Plan &pl, int sm_count) {
     if (pl.var->small) return small_smem_bytes(pl.src_packs_pad, pl.nslab, pl.var->T);
+    if (pl.var->balanced) return balanced_plan_smem(pl, sm_count);
     return pl.group_slabs > 1 ? pl.var->smem_grouped : pl.var->smem;
 }
 
@@ -639,7 +726,8 @@ static void make_plan(SimPipeline *sim, uint32_t forced_slab, bool exact) {
         if (pl.nslab > 8) NB_CUDA(cudaFuncSetAttribute(pl.var->func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     }
     int occ = 0;
-    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, plan_func(pl), pl.var->threads, plan_smem(pl)));
+    NB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, plan_func(pl), pl.var->threads,
+                                                          plan_smem(pl, sim->prop.multiProcessorCount)));
     NB_ASSERT(occ >= pl.var->minb, "kernel variant %s%s: %d CTAs/SM resident, %d planned", pl.var->name,
               pl.group_slabs > 1 ? " (grouped)" : "", occ, pl.var->minb);
     /* opt-in: n chained steps of a small World in one cooperative launch, only when the whole grid is co-resident */
@@ -1059,7 +1147,11 @@ static uint32_t aim_at_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_
 
 static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0, uint32_t t1) {
     if (t1 <= t0) return;
-    const uint32_t grid = aim_at_tiles(sim, sh, p, t0, t1);
+    uint32_t grid = aim_at_tiles(sim, sh, p, t0, t1);
+    if (sim->plan.var->balanced) { /* the units of rows [t0, t1) over at most one CTA per SM */
+        p.fold_tiles = t1 - t0;
+        grid = std::min<uint32_t>(grid, (uint32_t)sim->prop.multiProcessorCount);
+    }
     /* Programmatic dependent launch on every launch: the kernel releases its dependents after its pair
      * loop, so the next step's CTAs are scheduled into slots as they drain and have their prologue done when
      * the last partial lands.  (Released at kernel entry instead, the next step's CTAs were parked early on an

@@ -48,6 +48,24 @@ def test_slab_groups_bitwise_equal_across_gpu_counts(nb, oracle, monkeypatch, gp
     assert many.tobytes() == one.tobytes()
 
 
+@pytest.mark.parametrize("gpus", [2, 4])
+@pytest.mark.parametrize("n", [6000, 16384])
+def test_balanced_kernel_bitwise_equal_across_gpu_counts(nb, oracle, monkeypatch, n, gpus):
+    """balanced_kernel.cuh shares its (row, slab) units out per launch range; sharding changes the ranges and with
+    them which rows straddle a CTA boundary, never the summation order."""
+    if nb.device_count() < gpus:
+        pytest.skip(f"needs {gpus} GPUs")
+    from nbody_b200.api import FLAG_NO_PEER_STORE
+    monkeypatch.setenv("NBODY_VARIANT", "b16x2")
+    arr, m = oracle.partition(nb.make_galaxies(n, 2))
+    one, info1 = _run(nb, arr, m, 4, 0.01, local_gpus=1)
+    assert info1["variant"] == "b16x2"
+    many, _ = _run(nb, arr, m, 4, 0.01, local_gpus=gpus)
+    assert many.tobytes() == one.tobytes()
+    nccl, _ = _run(nb, arr, m, 4, 0.01, local_gpus=gpus, flags=FLAG_NO_PEER_STORE)
+    assert nccl.tobytes() == one.tobytes()
+
+
 def test_caller_device_is_restored(nb, oracle):
     """Advisor finding (round 1): the entry points used to leave the CUDA current device changed."""
     torch = pytest.importorskip("torch")

@@ -273,6 +273,35 @@ def test_small_world_kernel_equals_step_kernel_bitwise(nb, oracle, monkeypatch, 
     assert six_small.tobytes() == six_big.tobytes()
 
 
+@pytest.mark.parametrize("n", [1, 33, 250, 1000, 4003, 6000, 12000, 16384, 20000])
+@pytest.mark.parametrize("variant,slab", [("b16x2", 0), ("b16x2", 128), ("b32x1", 0), ("b16x4", 256), ("b16x1", 512)])
+def test_balanced_kernel_equals_step_kernel_bitwise(nb, oracle, monkeypatch, n, variant, slab):
+    """balanced_kernel.cuh shares (target row, slab) units out evenly over one CTA per SM: rows whose slabs all fall
+    into one CTA are added up in shared memory, rows that straddle a CTA boundary through the partial buffer and a
+    ticket.  Which CTA computed which unit must not show: same slab boundaries, same chains as step_kernel.cuh, the
+    same bits -- one step and chained steps, ragged sizes, massless tails, planned and forced slab lengths."""
+    arr, m = oracle.partition(nb.make_galaxies(n, 2) if n >= 250 else _cloud(n))
+    monkeypatch.setenv("NBODY_VARIANT", variant)
+    with nb.SimPipeline(n, m, slab_len=slab) as a:
+        info = a.info()
+        a.set_data(arr)
+        a.update(1, 0.01)
+        one_bal = a.get_data()
+        a.update(5, 0.02)
+        six_bal = a.get_data()
+    assert info["variant"] == variant and info["tile_targets"] == 32 * int(variant[-1])
+    monkeypatch.setenv("NBODY_VARIANT", "t128x2")
+    with nb.SimPipeline(n, m, slab_len=info["slab_len"]) as b:
+        assert b.info()["slab_len"] == info["slab_len"] and b.info()["slabs"] == info["slabs"]
+        b.set_data(arr)
+        b.update(1, 0.01)
+        one_big = b.get_data()
+        b.update(5, 0.02)
+        six_big = b.get_data()
+    assert one_bal.tobytes() == one_big.tobytes()
+    assert six_bal.tobytes() == six_big.tobytes()
+
+
 def _cloud(n):
     rng = np.random.default_rng(1000 + n)
     ps = np.zeros(n, dtype=PARTICLE)

@@ -12,12 +12,17 @@
  *
  *   - all sources are staged in shared memory once per CTA (TMA bulk copies, as in small_kernel.cuh); the targets of
  *     the rows a CTA touches (pos, vel, radius) are staged beside them at kernel entry, off the critical path;
- *   - warp w walks units w, w + WARPS, ... of the CTA's range with the same pair arithmetic and the same even/odd
- *     chains as the other kernels (interact_pack) and leaves each unit's even + odd sum in shared memory;
- *   - after one __syncthreads one warp per row finishes it: a row whose nslab units all belong to this CTA is added
- *     up in slab order from shared memory and integrated; a row that straddles a CTA boundary (at most two per CTA)
- *     goes through the global partial buffer and an arrival ticket exactly like step_kernel.cuh -- this CTA's slab
- *     sums are stored, and the last of the row's CTAs to arrive adds ALL nslab partials in slab order and integrates.
+ *   - the warps take units from a queue of the CTA's range (a shared-memory counter), compute them with the same
+ *     pair arithmetic and the same even/odd chains as the other kernels (interact_pack) and leave each unit's
+ *     even + odd sum in shared memory;
+ *   - no barrier after the pair loop: the warp that completes the last of the CTA's units of a row (a shared-memory
+ *     counter per row) finishes that row at once.  A row whose nslab units all belong to this CTA is added up in
+ *     slab order from shared memory and integrated.  A row that straddles a CTA boundary (at most two per CTA) goes
+ *     through the global partial buffer and an arrival ticket exactly like step_kernel.cuh -- this CTA's slab sums
+ *     are stored, and the last of the row's CTAs to arrive adds ALL nslab partials in slab order and integrates.
+ *     The units of those rows are first in the queue, so that chain of L2 round trips (store, ticket,
+ *     ceil(nslab / 16) rounds of loads: 3 ... 5 us at the end of the first version of this kernel) runs while the
+ *     other warps are still in their pair loops.
  *
  * The summation order is the plan's alone (slab boundaries, even/odd chains, slabs in order): which CTA computed
  * which unit does not enter, so the results are bit-identical to step_kernel.cuh and small_kernel.cuh with the same
@@ -46,11 +51,92 @@ __host__ __device__ inline BalancedGeom balanced_geom(uint32_t rows, uint32_t ns
 }
 
 /* dynamic shared memory: sources [src_packs_pad] x 48 B | unit sums [upc_max][32 T] float2 |
- * staged targets [rpc_max][32 T] x (pos, vel: float2; radius: float) | mbarrier */
+ * staged targets [rpc_max][32 T] x (pos, vel: float2; radius: float) | row counters [rpc_max] | mbarrier | queue */
 __host__ __device__ inline size_t balanced_smem_bytes(uint32_t src_packs_pad, uint32_t nslab, int T, uint32_t rows,
                                                       uint32_t ctas) {
     const BalancedGeom g = balanced_geom(rows, nslab, ctas);
-    return (size_t)src_packs_pad * 48 + (size_t)g.upc_max * 32 * T * sizeof(float2) + (size_t)g.rpc_max * 32 * T * 20 + 16;
+    return (size_t)src_packs_pad * 48 + (size_t)g.upc_max * 32 * T * sizeof(float2) + (size_t)g.rpc_max * 32 * T * 20 +
+           (size_t)((g.rpc_max + 1u) & ~1u) * sizeof(unsigned) + 16;
+}
+
+/* Finish one target row (the caller's warp just completed the last of this CTA's units of it): kept out of line so
+ * that its registers -- the partial loads of the straddling case -- do not weigh on the pair loop. */
+template <int T>
+__device__ __noinline__ void balanced_finish_row(const StepParams &p, const float2 *s_part, const float2 *row_vel,
+                                                 const float2 *row_pos, uint32_t row, uint32_t u0, uint32_t u1, uint32_t G,
+                                                 uint32_t units, uint32_t lane) {
+    constexpr int ROW = 32 * T;
+    const uint32_t ub = row * p.nslab;                       /* the row's unit of slab 0           */
+    const uint32_t s_lo = ub >= u0 ? 0u : u0 - ub;           /* this CTA holds slabs [s_lo, s_hi)  */
+    const uint32_t s_hi = min(p.nslab, u1 - ub);
+    const uint32_t tile = p.tile_first + row;
+    const uint32_t i0 = tile * ROW + lane;
+    /* this CTA's sum of slab s (s_lo <= s < s_hi) of the row, target k * 32 + lane */
+    auto mine = [&](uint32_t sl, int k) { return s_part[(size_t)(ub + sl - u0) * ROW + k * 32 + lane]; };
+    if (s_lo == 0 && s_hi == p.nslab) { /* the whole row is here: slab order, from shared memory */
+#pragma unroll
+        for (int k = 0; k < T; k++) {
+            float2 sum = mine(0, k);
+            for (uint32_t sl = 1; sl < p.nslab; sl++) {
+                const float2 v = mine(sl, k);
+                sum.x = __fadd_rn(sum.x, v.x);
+                sum.y = __fadd_rn(sum.y, v.y);
+            }
+            const uint32_t i = i0 + k * 32;
+            if (i < p.total_len) integrate_store_vx(p, i, sum, row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
+        }
+        return;
+    }
+    /* the row straddles a CTA boundary: publish this CTA's slab sums, take a ticket */
+    for (uint32_t sl = s_lo; sl < s_hi; sl++) {
+#pragma unroll
+        for (int k = 0; k < T; k++) __stcg(&p.part[(size_t)sl * p.part_stride + i0 + k * 32], mine(sl, k));
+    }
+    __threadfence();
+    __syncwarp();
+    int last = 0;
+    if (lane == 0) {
+        /* unit u belongs to CTA ceil((u + 1) G / U) - 1 */
+        const uint32_t c_first = (uint32_t)((((uint64_t)ub + 1) * G + units - 1) / units) - 1;
+        const uint32_t c_last = (uint32_t)((((uint64_t)ub + p.nslab) * G + units - 1) / units) - 1;
+        const unsigned ticket = atomicAdd(&p.tile_cnt[tile], 1u);
+        last = (ticket == c_last - c_first);
+        if (last) p.tile_cnt[tile] = 0; /* ready for the next step */
+    }
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    __threadfence();
+    /* last CTA of this row: all slab partials in slab order; RB slabs of all T targets in flight together */
+    constexpr int RB = T <= 2 ? 16 : 8;
+    float2 sum[T];
+    for (uint32_t s0 = 0; s0 < p.nslab; s0 += RB) {
+        float2 v[T][RB];
+#pragma unroll
+        for (int k = 0; k < T; k++) {
+#pragma unroll
+            for (int w = 0; w < RB; w++)
+                if (s0 + w < p.nslab) v[k][w] = __ldcg(&p.part[(size_t)(s0 + w) * p.part_stride + i0 + k * 32]);
+        }
+#pragma unroll
+        for (int k = 0; k < T; k++) {
+#pragma unroll
+            for (int w = 0; w < RB; w++) {
+                if (s0 + w < p.nslab) {
+                    if (s0 + w == 0) {
+                        sum[k] = v[k][0];
+                    } else {
+                        sum[k].x = __fadd_rn(sum[k].x, v[k][w].x);
+                        sum[k].y = __fadd_rn(sum[k].y, v[k][w].y);
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < T; k++) {
+        const uint32_t i = i0 + k * 32;
+        if (i < p.total_len) integrate_store_vx(p, i, sum[k], row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
+    }
 }
 
 /* StepParams as the other kernels see it; fold_tiles carries the number of target rows of this launch. */
@@ -67,19 +153,33 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     float2 *s_tpos = s_part + (size_t)geo.upc_max * ROW;                  /* [rpc_max][ROW]     */
     float2 *s_tvel = s_tpos + (size_t)geo.rpc_max * ROW;
     float *s_trad = reinterpret_cast<float *>(s_tvel + (size_t)geo.rpc_max * ROW);
-    uint64_t *bar = reinterpret_cast<uint64_t *>(s_trad + (size_t)geo.rpc_max * ROW);
+    unsigned *s_rowcnt = reinterpret_cast<unsigned *>(s_trad + (size_t)geo.rpc_max * ROW); /* [rpc_max] units done per row */
+    uint64_t *bar = reinterpret_cast<uint64_t *>(s_rowcnt + ((geo.rpc_max + 1u) & ~1u));
+    unsigned *s_next = reinterpret_cast<unsigned *>(bar + 1);             /* the CTA's unit queue */
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     /* this CTA's units, and the rows (launch-local numbers) they belong to */
     const uint32_t u0 = (uint32_t)((uint64_t)blockIdx.x * geo.units / G);
     const uint32_t u1 = (uint32_t)((uint64_t)(blockIdx.x + 1) * geo.units / G);
+    const uint32_t L = u1 - u0;
     const uint32_t row_first = u0 / p.nslab;
     const uint32_t nrow = (u1 - 1) / p.nslab - row_first + 1;
+    /* Queue order: the units of the rows this CTA shares with a neighbour come first -- the head of the range when
+     * it starts inside a row, then the tail when it ends inside one -- so that their slab sums are published, and
+     * the row finished by whichever CTA comes last, while the rest of the pair loop is still running. */
+    const uint32_t head_end = min((row_first + 1) * p.nslab, u1) - u0;   /* units of the first row       */
+    const bool head_split = head_end < p.nslab;                           /* ... which is not whole here  */
+    const uint32_t n_head = head_split ? head_end : 0u;
+    const uint32_t tail_begin = max(((u1 - 1) / p.nslab) * p.nslab, u0) - u0;
+    const bool tail_split = nrow > 1 && (L - tail_begin) < p.nslab;
+    const uint32_t n_tail = tail_split ? L - tail_begin : 0u;
 
     if (tid == 0) {
         mbar_init(bar, 1);
+        *s_next = WARPS; /* the first WARPS queue entries are taken by warp number */
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (uint32_t k = tid; k < nrow; k += WARPS * 32) s_rowcnt[k] = 0;
     __syncthreads();
     /* programmatic dependent launch: nothing global before the previous step's writes are visible */
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -113,116 +213,65 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     __syncthreads();
     mbar_wait(bar, 0);
 
-    for (uint32_t ul = warp; ul < u1 - u0; ul += WARPS) {
+    for (uint32_t q = warp; q < L;) {
+        /* queue entry -> unit of the range: head units, tail units, then the middle */
+        const uint32_t ul = q < n_head ? q : q < n_head + n_tail ? tail_begin + (q - n_head) : q - n_tail;
         const uint32_t u = u0 + ul;
         const uint32_t row = u / p.nslab, s = u - row * p.nslab;
-        const uint32_t t = (row - row_first) * ROW + lane;
-        float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
+        const uint32_t rc = row - row_first;
+        const uint32_t t = rc * ROW + lane;
+        {
+            float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
 #pragma unroll
-        for (int k = 0; k < T; k++) {
-            const float2 x = s_tpos[t + k * 32];
-            const float r = s_trad[t + k * 32];
-            ntx[k] = make_float2(-x.x, -x.x);
-            nty[k] = make_float2(-x.y, -x.y);
-            rho[k] = make_float2(r, r);
-            ax[k] = make_float2(0.f, 0.f);
-            ay[k] = make_float2(0.f, 0.f);
-        }
-        const uint32_t pk0 = s * p.slab_packs;
-        const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
-#pragma unroll 1
-        for (uint32_t q = pk0; q < pk1; q += UNR) {
-#pragma unroll
-            for (int w = 0; w < UNR; w++) {
-                const float4 xs = s_xy[2 * (q + w)];
-                const float4 ys = s_xy[2 * (q + w) + 1];
-                const float4 gs = s_gm[q + w];
-                interact_pack<T, kFormPacked>(xs, ys, gs, ntx, nty, rho, ax, ay);
+            for (int k = 0; k < T; k++) {
+                const float2 x = s_tpos[t + k * 32];
+                const float r = s_trad[t + k * 32];
+                ntx[k] = make_float2(-x.x, -x.x);
+                nty[k] = make_float2(-x.y, -x.y);
+                rho[k] = make_float2(r, r);
+                ax[k] = make_float2(0.f, 0.f);
+                ay[k] = make_float2(0.f, 0.f);
             }
-        }
+            const uint32_t pk0 = s * p.slab_packs;
+            const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
+#pragma unroll 1
+            for (uint32_t pk = pk0; pk < pk1; pk += UNR) {
 #pragma unroll
-        for (int k = 0; k < T; k++)
-            s_part[(size_t)ul * ROW + k * 32 + lane] = make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
-    }
+                for (int w = 0; w < UNR; w++) {
+                    const float4 xs = s_xy[2 * (pk + w)];
+                    const float4 ys = s_xy[2 * (pk + w) + 1];
+                    const float4 gs = s_gm[pk + w];
+                    interact_pack<T, kFormPacked>(xs, ys, gs, ntx, nty, rho, ax, ay);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < T; k++)
+                s_part[(size_t)ul * ROW + k * 32 + lane] =
+                    make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+        }
 
-    /* pair loop done: the next step's grid may be scheduled into the slots that free up from here on */
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    __syncthreads();
-
-    /* finish the rows: one warp per row */
-    for (uint32_t rc = warp; rc < nrow; rc += WARPS) {
-        const uint32_t row = row_first + rc;
+        /* the warp that completes the last of this CTA's units of a row finishes the row; everyone takes the next
+         * queue entry */
         const uint32_t ub = row * p.nslab;                       /* the row's unit of slab 0           */
         const uint32_t s_lo = ub >= u0 ? 0u : u0 - ub;           /* this CTA holds slabs [s_lo, s_hi)  */
         const uint32_t s_hi = min(p.nslab, u1 - ub);
-        const uint32_t tile = p.tile_first + row;
-        const uint32_t i0 = tile * ROW + lane;
-        /* this CTA's sum of slab s (s_lo <= s < s_hi) of the row, target k * 32 + lane */
-        auto mine = [&](uint32_t s, int k) { return s_part[(size_t)(ub + s - u0) * ROW + k * 32 + lane]; };
-        if (s_lo == 0 && s_hi == p.nslab) {
-#pragma unroll
-            for (int k = 0; k < T; k++) {
-                float2 sum = mine(0, k);
-                for (uint32_t s = 1; s < p.nslab; s++) {
-                    const float2 v = mine(s, k);
-                    sum.x = __fadd_rn(sum.x, v.x);
-                    sum.y = __fadd_rn(sum.y, v.y);
-                }
-                const uint32_t i = i0 + k * 32;
-                if (i < p.total_len) integrate_store_vx(p, i, sum, s_tvel[rc * ROW + k * 32 + lane], s_tpos[rc * ROW + k * 32 + lane]);
-            }
-            continue;
-        }
-        /* the row straddles a CTA boundary: publish this CTA's slab sums, take a ticket */
-        for (uint32_t s = s_lo; s < s_hi; s++) {
-#pragma unroll
-            for (int k = 0; k < T; k++) __stcg(&p.part[(size_t)s * p.part_stride + i0 + k * 32], mine(s, k));
-        }
-        __threadfence();
         __syncwarp();
-        int last = 0;
+        unsigned done = 0, qn = 0;
         if (lane == 0) {
-            /* unit u belongs to CTA ceil((u + 1) G / U) - 1 */
-            const uint32_t c_first = (uint32_t)((((uint64_t)ub + 1) * G + geo.units - 1) / geo.units) - 1;
-            const uint32_t c_last = (uint32_t)((((uint64_t)ub + p.nslab) * G + geo.units - 1) / geo.units) - 1;
-            const unsigned ticket = atomicAdd(&p.tile_cnt[tile], 1u);
-            last = (ticket == c_last - c_first);
-            if (last) p.tile_cnt[tile] = 0; /* ready for the next step */
+            __threadfence_block();
+            done = atomicAdd(&s_rowcnt[rc], 1u) + 1u == s_hi - s_lo;
+            qn = atomicAdd(s_next, 1u);
         }
-        last = __shfl_sync(0xffffffffu, last, 0);
-        if (!last) continue;
-        __threadfence();
-        /* last CTA of this row: all slab partials in slab order; 8 slabs of all T targets in flight together */
-        float2 sum[T];
-        for (uint32_t s0 = 0; s0 < p.nslab; s0 += 8) {
-            float2 v[T][8];
-#pragma unroll
-            for (int k = 0; k < T; k++) {
-#pragma unroll
-                for (int w = 0; w < 8; w++)
-                    if (s0 + w < p.nslab) v[k][w] = __ldcg(&p.part[(size_t)(s0 + w) * p.part_stride + i0 + k * 32]);
-            }
-#pragma unroll
-            for (int k = 0; k < T; k++) {
-#pragma unroll
-                for (int w = 0; w < 8; w++) {
-                    if (s0 + w < p.nslab) {
-                        if (s0 + w == 0) {
-                            sum[k] = v[k][0];
-                        } else {
-                            sum[k].x = __fadd_rn(sum[k].x, v[k][w].x);
-                            sum[k].y = __fadd_rn(sum[k].y, v[k][w].y);
-                        }
-                    }
-                }
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < T; k++) {
-            const uint32_t i = i0 + k * 32;
-            if (i < p.total_len) integrate_store_vx(p, i, sum[k], s_tvel[rc * ROW + k * 32 + lane], s_tpos[rc * ROW + k * 32 + lane]);
-        }
+        done = __shfl_sync(0xffffffffu, done, 0);
+        q = __shfl_sync(0xffffffffu, qn, 0);
+        if (!done) continue;
+        __threadfence_block();
+
+        balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row, u0, u1, G, geo.units, lane);
     }
+
+    /* this thread's pair loops are done: once every thread is here the next step's grid may be scheduled */
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 }  // namespace nb

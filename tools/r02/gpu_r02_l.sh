@@ -4,12 +4,12 @@
 set -u
 OUT=gpurun_out; mkdir -p $OUT
 timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "balanced" > $OUT/r02l_balanced_tests.log 2>&1; echo "pytest rc=$?" >> $OUT/r02l_balanced_tests.log; tail -5 $OUT/r02l_balanced_tests.log
-SIZES="2000 4000 4736 6000 8000 10000 12000 14208 16384 18944 20000 24000 28000 32000"
+SIZES=${SIZES:-"2000 4000 4736 6000 8000 10000 12000 14208 16384 18944 20000 24000 28000 32000"}
 B=nbody_b200/bin/nbody-bench
 {
 echo "== shipped"
 for n in $SIZES; do timeout 60 $B --gpu --fresh-seed --n $n | tail -1; done
-for v in b16x2 b32x1 b16x1 b16x4 b8x4 b32x2; do
+for v in ${VARIANTS:-b16x2 b32x1 b16x1 b16x4 b8x4 b32x2}; do
   for s in 0 128 256 512; do
     echo "== $v slab $s"
     for n in $SIZES; do NBODY_VARIANT=$v NBODY_SLAB=$s timeout 60 $B --gpu --fresh-seed --n $n 2>&1 | tail -1; done

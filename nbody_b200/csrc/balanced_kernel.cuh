@@ -140,7 +140,9 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
 }
 
 /* StepParams as the other kernels see it; fold_tiles carries the number of target rows of this launch. */
-template <int WARPS, int T, int UNR>
+/* MODE: experiment switches (bit 0: units by warp number in rounds instead of the queue; bit 1: natural unit order;
+ * bit 2: whole rows finished after a CTA barrier, one warp per row) */
+template <int WARPS, int T, int UNR, int MODE = 0>
 __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_constant__ StepParams p) {
     constexpr int ROW = 32 * T;
     const uint32_t G = gridDim.x;
@@ -169,10 +171,10 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
      * the row finished by whichever CTA comes last, while the rest of the pair loop is still running. */
     const uint32_t head_end = min((row_first + 1) * p.nslab, u1) - u0;   /* units of the first row       */
     const bool head_split = head_end < p.nslab;                           /* ... which is not whole here  */
-    const uint32_t n_head = head_split ? head_end : 0u;
+    const uint32_t n_head = (head_split && !(MODE & 2)) ? head_end : 0u;
     const uint32_t tail_begin = max(((u1 - 1) / p.nslab) * p.nslab, u0) - u0;
     const bool tail_split = nrow > 1 && (L - tail_begin) < p.nslab;
-    const uint32_t n_tail = tail_split ? L - tail_begin : 0u;
+    const uint32_t n_tail = (tail_split && !(MODE & 2)) ? L - tail_begin : 0u;
 
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -260,10 +262,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
         if (lane == 0) {
             __threadfence_block();
             done = atomicAdd(&s_rowcnt[rc], 1u) + 1u == s_hi - s_lo;
-            qn = atomicAdd(s_next, 1u);
+            if (!(MODE & 1)) qn = atomicAdd(s_next, 1u);
         }
         done = __shfl_sync(0xffffffffu, done, 0);
-        q = __shfl_sync(0xffffffffu, qn, 0);
+        if (MODE & 1) q += WARPS;
+        else q = __shfl_sync(0xffffffffu, qn, 0);
+        if ((MODE & 4) && s_lo == 0 && s_hi == p.nslab) continue;
         if (!done) continue;
         __threadfence_block();
 
@@ -272,6 +276,14 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
 
     /* this thread's pair loops are done: once every thread is here the next step's grid may be scheduled */
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (MODE & 4) {
+        __syncthreads();
+        for (uint32_t rc = warp; rc < nrow; rc += WARPS) {
+            const uint32_t row = row_first + rc, ub = row * p.nslab;
+            if (ub >= u0 && ub + p.nslab <= u1)
+                balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row, u0, u1, G, geo.units, lane);
+        }
+    }
 }
 
 }  // namespace nb

@@ -93,7 +93,7 @@ static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bo
 }
 
 /* GRID CTAs (at most one per SM) share out p.fold_tiles rows x p.nslab slabs */
-template <int WARPS, int T, int UNR>
+template <int WARPS, int T, int UNR, int MODE = 0>
 static void launch_balanced(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
@@ -109,7 +109,7 @@ static void launch_balanced(uint32_t grid, cudaStream_t st, const StepParams &p,
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    NB_CUDA(cudaLaunchKernelEx(&cfg, balanced_kernel<WARPS, T, UNR>, p));
+    NB_CUDA(cudaLaunchKernelEx(&cfg, balanced_kernel<WARPS, T, UNR, MODE>, p));
 }
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
@@ -181,10 +181,10 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
             launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true, false, false           \
     }
 /* the balanced kernel of mid-size Worlds: WARPS warps per CTA, T targets per lane, one CTA per SM */
-#define NB_VARIANT_BALANCED(NAME, WARPS, T, UNR)                                                             \
+#define NB_VARIANT_BALANCED(NAME, WARPS, T, UNR, MODE)                                                       \
     {                                                                                                        \
-        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)balanced_kernel<WARPS, T, UNR>,     \
-            launch_balanced<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, false, false, true        \
+        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)balanced_kernel<WARPS, T, UNR, MODE>, \
+            launch_balanced<WARPS, T, UNR, MODE>, 0, nullptr, nullptr, nullptr, nullptr, false, false, true  \
     }
 /* the reference-exact verification kernel for the reference build with LANES SIMD lanes */
 #define NB_VARIANT_EXACT(NAME, LANES)                                                                        \
@@ -216,12 +216,17 @@ static const Variant kVariants[] = {
     NB_VARIANT_SMALL("w16x1", 16, 1, 2), /* NBODY_VARIANT only (the sweep's other candidates) */
     NB_VARIANT_SMALL("w8x1", 8, 1, 2),
     /* mid-size Worlds: (row, slab) units shared out evenly over one CTA per SM (balanced_kernel.cuh) */
-    NB_VARIANT_BALANCED("b16x2", 16, 2, 2),
-    NB_VARIANT_BALANCED("b16x1", 16, 1, 2),
-    NB_VARIANT_BALANCED("b32x1", 32, 1, 2),
-    NB_VARIANT_BALANCED("b16x4", 16, 4, 2),
-    NB_VARIANT_BALANCED("b8x4", 8, 4, 2),
-    NB_VARIANT_BALANCED("b32x2", 32, 2, 2),
+    NB_VARIANT_BALANCED("b16x2", 16, 2, 2, 0),
+    NB_VARIANT_BALANCED("b16x1", 16, 1, 2, 0),
+    NB_VARIANT_BALANCED("b32x1", 32, 1, 2, 0),
+    NB_VARIANT_BALANCED("b16x4", 16, 4, 2, 0),
+    NB_VARIANT_BALANCED("b8x4", 8, 4, 2, 0),
+    NB_VARIANT_BALANCED("b32x2", 32, 2, 2, 0),
+    NB_VARIANT_BALANCED("b16x2m1", 16, 2, 2, 1),
+    NB_VARIANT_BALANCED("b16x2m2", 16, 2, 2, 2),
+    NB_VARIANT_BALANCED("b16x2m4", 16, 2, 2, 4),
+    NB_VARIANT_BALANCED("b16x2m7", 16, 2, 2, 7),
+    NB_VARIANT_BALANCED("b16x4m7", 16, 4, 2, 7),
     /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
      * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
     NB_VARIANT_EXACT("ref8", 8),

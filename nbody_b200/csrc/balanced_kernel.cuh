@@ -59,6 +59,39 @@ __host__ __device__ inline size_t balanced_smem_bytes(uint32_t src_packs_pad, ui
            (size_t)((g.rpc_max + 1u) & ~1u) * sizeof(unsigned) + 16;
 }
 
+/* integrate_store_vx with every field of the parameter block already in registers (RowOut).  Inside the out-of-line
+ * balanced_finish_row the block is reached through a generic pointer, and the compiler must assume that each of our
+ * stores may have changed it: with the fields read through that pointer where they are used, every store was followed
+ * by dependent re-loads of part / part_stride / pos / vel / ... (measured: +4.7 us per step at T = 2, +8.5 us at T = 4). */
+struct RowOut {
+    float2 *pos, *vel, *acc;
+    float *dst0;
+    float *const *dst_xy;
+    int ndst;
+    uint32_t total_len, mass_len;
+    float dt;
+};
+__device__ __forceinline__ void row_integrate_store(const RowOut &o, uint32_t i, float2 a, float2 v, float2 x) {
+    v.x = __fadd_rn(v.x, __fmul_rn(a.x, o.dt));
+    v.y = __fadd_rn(v.y, __fmul_rn(a.y, o.dt));
+    x.x = __fadd_rn(x.x, __fmul_rn(v.x, o.dt));
+    x.y = __fadd_rn(x.y, __fmul_rn(v.y, o.dt));
+    o.acc[i] = a;
+    o.vel[i] = v;
+    o.pos[i] = x;
+    if (i < o.mass_len) {
+        const uint32_t w = (i >> 2) * 8u + (i & 3u);
+        o.dst0[w] = x.x;
+        o.dst0[w + 4] = x.y;
+#pragma unroll 1
+        for (int d = 1; d < o.ndst; d++) { /* peer GPUs */
+            float *dst = o.dst_xy[d];
+            dst[w] = x.x;
+            dst[w + 4] = x.y;
+        }
+    }
+}
+
 /* Finish one target row (the caller's warp just completed the last of this CTA's units of it): kept out of line so
  * that its registers -- the partial loads of the straddling case -- do not weigh on the pair loop. */
 template <int T>
@@ -66,31 +99,36 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
                                                  const float2 *row_pos, uint32_t row, uint32_t u0, uint32_t u1, uint32_t G,
                                                  uint32_t units, uint32_t lane) {
     constexpr int ROW = 32 * T;
-    const uint32_t ub = row * p.nslab;                       /* the row's unit of slab 0           */
+    /* the parameter block, once */
+    const RowOut out = {p.pos, p.vel, p.acc, p.dst_xy[0], p.dst_xy, p.ndst, p.total_len, p.mass_len, p.dt};
+    float2 *const part = p.part;
+    unsigned *const tile_cnt = p.tile_cnt;
+    const uint32_t nslab = p.nslab, part_stride = p.part_stride;
+    const uint32_t ub = row * nslab;                         /* the row's unit of slab 0           */
     const uint32_t s_lo = ub >= u0 ? 0u : u0 - ub;           /* this CTA holds slabs [s_lo, s_hi)  */
-    const uint32_t s_hi = min(p.nslab, u1 - ub);
+    const uint32_t s_hi = min(nslab, u1 - ub);
     const uint32_t tile = p.tile_first + row;
     const uint32_t i0 = tile * ROW + lane;
     /* this CTA's sum of slab s (s_lo <= s < s_hi) of the row, target k * 32 + lane */
     auto mine = [&](uint32_t sl, int k) { return s_part[(size_t)(ub + sl - u0) * ROW + k * 32 + lane]; };
-    if (s_lo == 0 && s_hi == p.nslab) { /* the whole row is here: slab order, from shared memory */
+    if (s_lo == 0 && s_hi == nslab) { /* the whole row is here: slab order, from shared memory */
 #pragma unroll
         for (int k = 0; k < T; k++) {
             float2 sum = mine(0, k);
-            for (uint32_t sl = 1; sl < p.nslab; sl++) {
+            for (uint32_t sl = 1; sl < nslab; sl++) {
                 const float2 v = mine(sl, k);
                 sum.x = __fadd_rn(sum.x, v.x);
                 sum.y = __fadd_rn(sum.y, v.y);
             }
             const uint32_t i = i0 + k * 32;
-            if (i < p.total_len) integrate_store_vx(p, i, sum, row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
+            if (i < out.total_len) row_integrate_store(out, i, sum, row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
         }
         return;
     }
     /* the row straddles a CTA boundary: publish this CTA's slab sums, take a ticket */
     for (uint32_t sl = s_lo; sl < s_hi; sl++) {
 #pragma unroll
-        for (int k = 0; k < T; k++) __stcg(&p.part[(size_t)sl * p.part_stride + i0 + k * 32], mine(sl, k));
+        for (int k = 0; k < T; k++) __stcg(&part[(size_t)sl * part_stride + i0 + k * 32], mine(sl, k));
     }
     __threadfence();
     __syncwarp();
@@ -98,10 +136,10 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
     if (lane == 0) {
         /* unit u belongs to CTA ceil((u + 1) G / U) - 1 */
         const uint32_t c_first = (uint32_t)((((uint64_t)ub + 1) * G + units - 1) / units) - 1;
-        const uint32_t c_last = (uint32_t)((((uint64_t)ub + p.nslab) * G + units - 1) / units) - 1;
-        const unsigned ticket = atomicAdd(&p.tile_cnt[tile], 1u);
+        const uint32_t c_last = (uint32_t)((((uint64_t)ub + nslab) * G + units - 1) / units) - 1;
+        const unsigned ticket = atomicAdd(&tile_cnt[tile], 1u);
         last = (ticket == c_last - c_first);
-        if (last) p.tile_cnt[tile] = 0; /* ready for the next step */
+        if (last) tile_cnt[tile] = 0; /* ready for the next step */
     }
     last = __shfl_sync(0xffffffffu, last, 0);
     if (!last) return;
@@ -109,19 +147,19 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
     /* last CTA of this row: all slab partials in slab order; RB slabs of all T targets in flight together */
     constexpr int RB = T <= 2 ? 16 : 8;
     float2 sum[T];
-    for (uint32_t s0 = 0; s0 < p.nslab; s0 += RB) {
+    for (uint32_t s0 = 0; s0 < nslab; s0 += RB) {
         float2 v[T][RB];
 #pragma unroll
         for (int k = 0; k < T; k++) {
 #pragma unroll
             for (int w = 0; w < RB; w++)
-                if (s0 + w < p.nslab) v[k][w] = __ldcg(&p.part[(size_t)(s0 + w) * p.part_stride + i0 + k * 32]);
+                if (s0 + w < nslab) v[k][w] = __ldcg(&part[(size_t)(s0 + w) * part_stride + i0 + k * 32]);
         }
 #pragma unroll
         for (int k = 0; k < T; k++) {
 #pragma unroll
             for (int w = 0; w < RB; w++) {
-                if (s0 + w < p.nslab) {
+                if (s0 + w < nslab) {
                     if (s0 + w == 0) {
                         sum[k] = v[k][0];
                     } else {
@@ -135,7 +173,7 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
 #pragma unroll
     for (int k = 0; k < T; k++) {
         const uint32_t i = i0 + k * 32;
-        if (i < p.total_len) integrate_store_vx(p, i, sum[k], row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
+        if (i < out.total_len) row_integrate_store(out, i, sum[k], row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
     }
 }
 

@@ -191,6 +191,11 @@ void NbSimRenderRGBA(SimPipeline *sim, int32_t width, int32_t height, float targ
  * as (ax, ay) doubles to OUT (2 * (last - first) values).  Does not advance the state. */
 void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out);
 
+/* Diagnostics for tools/step_timeline.py: the kernel variants built with the timeline switch (NBODY_VARIANT=b16x2t ...)
+ * record %globaltimer (ns) per warp at four points of a step -- after the dependency wait, sources in shared memory,
+ * last unit done, end.  Copies [warps][4] values of the last such launch on the current device; returns the warps. */
+uint32_t NbSimDebugTimeline(uint64_t *out, uint32_t max_warps);
+
 #ifdef __cplusplus
 }
 #endif

@@ -136,6 +136,7 @@ def lib():
         "NbSimPlan": (None, [u32, u32, C.c_int32, C.c_int32, C.POINTER(SimPlanInfo), vp]),
         "NbSimDiagnostics": (None, [vp, vp]),
         "NbSimAccF64": (None, [vp, u32, u32, vp]),
+        "NbSimDebugTimeline": (u32, [vp, u32]),
         "NbSimFitCamera": (None, [vp, C.c_int32, C.c_int32, C.POINTER(f32), C.POINTER(f32), C.POINTER(f32)]),
         "NbSimRenderRGBA": (None, [vp, C.c_int32, C.c_int32, f32, f32, f32, f32, vp]),
         # world.c extras

@@ -179,7 +179,7 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
 
 /* StepParams as the other kernels see it; fold_tiles carries the number of target rows of this launch. */
 /* MODE: experiment switches (bit 0: units by warp number in rounds instead of the queue; bit 1: natural unit order;
- * bit 2: whole rows finished after a CTA barrier, one warp per row) */
+ * bit 2: whole rows finished after a CTA barrier, one warp per row; bit 3: record the timeline) */
 template <int WARPS, int T, int UNR, int MODE = 0>
 __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_constant__ StepParams p) {
     constexpr int ROW = 32 * T;
@@ -223,6 +223,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     __syncthreads();
     /* programmatic dependent launch: nothing global before the previous step's writes are visible */
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    constexpr bool TL = (MODE & 8) != 0;
+    const uint32_t tl_slot = blockIdx.x * WARPS + warp;
+    timeline_mark(TL, tl_slot, 0);
 
     if (tid == 0) { /* all sources -> shared memory; bulk copies of at most 32 KB each */
         const uint32_t xy_bytes = p.src_packs_pad * 32u, gm_bytes = p.src_packs_pad * 16u;
@@ -252,6 +255,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     }
     __syncthreads();
     mbar_wait(bar, 0);
+    timeline_mark(TL, tl_slot, 1);
+    timeline_mark(TL, tl_slot, 2); /* warps without a unit */
 
     for (uint32_t q = warp; q < L;) {
         /* queue entry -> unit of the range: head units, tail units, then the middle */
@@ -303,6 +308,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
             if (!(MODE & 1)) qn = atomicAdd(s_next, 1u);
         }
         done = __shfl_sync(0xffffffffu, done, 0);
+        timeline_mark(TL, tl_slot, 2);
         if (MODE & 1) q += WARPS;
         else q = __shfl_sync(0xffffffffu, qn, 0);
         if ((MODE & 4) && s_lo == 0 && s_hi == p.nslab) continue;
@@ -314,6 +320,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
 
     /* this thread's pair loops are done: once every thread is here the next step's grid may be scheduled */
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (!(MODE & 4)) timeline_mark(TL, tl_slot, 3);
     if (MODE & 4) {
         __syncthreads();
         for (uint32_t rc = warp; rc < nrow; rc += WARPS) {
@@ -321,6 +328,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
             if (ub >= u0 && ub + p.nslab <= u1)
                 balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row, u0, u1, G, geo.units, lane);
         }
+        timeline_mark(TL, tl_slot, 3);
     }
 }
 

@@ -73,7 +73,7 @@ static void launch_exact(uint32_t grid, cudaStream_t st, const StepParams &p, bo
     NB_CUDA(cudaLaunchKernelEx(&cfg, exact_kernel<LANES>, p));
 }
 
-template <int WARPS, int T, int UNR>
+template <int WARPS, int T, int UNR, bool TL = false>
 static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
@@ -89,7 +89,7 @@ static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bo
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    NB_CUDA(cudaLaunchKernelEx(&cfg, small_world_kernel<WARPS, T, UNR>, p));
+    NB_CUDA(cudaLaunchKernelEx(&cfg, small_world_kernel<WARPS, T, UNR, TL>, p));
 }
 
 /* GRID CTAs (at most one per SM) share out p.fold_tiles rows x p.nslab slabs */
@@ -175,10 +175,11 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
             false, false, false                                                                              \
     }
 /* the small-World kernel: WARPS warps per CTA, T targets per lane; TJP only rounds the source padding */
-#define NB_VARIANT_SMALL(NAME, WARPS, T, UNR)                                                                \
+#define NB_VARIANT_SMALL(NAME, WARPS, T, UNR) NB_VARIANT_SMALL_TL(NAME, WARPS, T, UNR, false)
+#define NB_VARIANT_SMALL_TL(NAME, WARPS, T, UNR, TL)                                                         \
     {                                                                                                        \
-        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)small_world_kernel<WARPS, T, UNR>,  \
-            launch_small<WARPS, T, UNR>, 0, nullptr, nullptr, nullptr, nullptr, true, false, false           \
+        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)small_world_kernel<WARPS, T, UNR, TL>, \
+            launch_small<WARPS, T, UNR, TL>, 0, nullptr, nullptr, nullptr, nullptr, true, false, false       \
     }
 /* the balanced kernel of mid-size Worlds: WARPS warps per CTA, T targets per lane, one CTA per SM */
 #define NB_VARIANT_BALANCED(NAME, WARPS, T, UNR, MODE)                                                       \
@@ -215,6 +216,9 @@ static const Variant kVariants[] = {
     NB_VARIANT_SMALL("w16x4", 16, 4, 2), /* planned: 0.78 x 128 SMs <= N <= 128 SMs */
     NB_VARIANT_SMALL("w16x1", 16, 1, 2), /* NBODY_VARIANT only (the sweep's other candidates) */
     NB_VARIANT_SMALL("w8x1", 8, 1, 2),
+    NB_VARIANT_SMALL_TL("w16x4t", 16, 4, 2, true), /* with the per-warp timeline (tools/step_timeline.py) */
+    NB_VARIANT_SMALL_TL("w16x3t", 16, 3, 2, true),
+    NB_VARIANT_SMALL_TL("w32x1t", 32, 1, 2, true),
     /* mid-size Worlds: (row, slab) units shared out evenly over one CTA per SM (balanced_kernel.cuh) */
     NB_VARIANT_BALANCED("b16x2", 16, 2, 2, 0),
     NB_VARIANT_BALANCED("b16x1", 16, 1, 2, 0),
@@ -227,6 +231,9 @@ static const Variant kVariants[] = {
     NB_VARIANT_BALANCED("b16x2m4", 16, 2, 2, 4),
     NB_VARIANT_BALANCED("b16x2m7", 16, 2, 2, 7),
     NB_VARIANT_BALANCED("b16x4m7", 16, 4, 2, 7),
+    NB_VARIANT_BALANCED("b16x2t", 16, 2, 2, 8),   /* with the per-warp timeline (tools/step_timeline.py) */
+    NB_VARIANT_BALANCED("b16x2m7t", 16, 2, 2, 15),
+    NB_VARIANT_BALANCED("b16x2m2t", 16, 2, 2, 10),
     /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
      * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
     NB_VARIANT_EXACT("ref8", 8),
@@ -1584,6 +1591,12 @@ void NbSimRenderRGBA(SimPipeline *sim, int32_t width, int32_t height, float targ
     NB_CUDA(cudaStreamSynchronize(sh.stream));
     NB_CUDA(cudaFree(winner));
     NB_CUDA(cudaFree(img));
+}
+
+uint32_t NbSimDebugTimeline(uint64_t *out, uint32_t max_warps) {
+    const uint32_t n = std::min<uint32_t>(max_warps, nb::kTimelineWarps);
+    NB_CUDA(cudaMemcpyFromSymbol(out, nb::nb_timeline, (size_t)n * 4 * sizeof(uint64_t)));
+    return n;
 }
 
 void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out) {

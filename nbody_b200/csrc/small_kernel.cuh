@@ -31,6 +31,18 @@ __host__ __device__ inline size_t small_smem_bytes(uint32_t src_packs_pad, uint3
     return (size_t)src_packs_pad * 48 + (size_t)nslab * 32 * T * sizeof(float2) + 16;
 }
 
+/* Diagnostics (kernels built with the timeline switch; tools/step_timeline.py): %globaltimer of every warp after the dependency wait, after the
+ * sources landed, after its last unit, and at its end. */
+constexpr uint32_t kTimelineWarps = 160 * 32;
+__device__ unsigned long long nb_timeline[kTimelineWarps * 4];
+__device__ __forceinline__ void timeline_mark(bool on, uint32_t slot, int what) {
+    if (on && (threadIdx.x & 31u) == 0 && slot < kTimelineWarps) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        nb_timeline[slot * 4 + what] = t;
+    }
+}
+
 /* integrate_store (force_kernel.cuh) with pos and vel already in registers */
 __device__ __forceinline__ void integrate_store_vx(const StepParams &p, uint32_t i, float2 a, float2 v, float2 x) {
     v.x = __fadd_rn(v.x, __fmul_rn(a.x, p.dt));
@@ -50,7 +62,7 @@ __device__ __forceinline__ void integrate_store_vx(const StepParams &p, uint32_t
     }
 }
 
-template <int WARPS, int T, int UNR>
+template <int WARPS, int T, int UNR, bool TL = false>
 __global__ void __launch_bounds__(WARPS * 32, 1) small_world_kernel(const __grid_constant__ StepParams p) {
     constexpr int TILE = 32 * T;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -70,6 +82,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_world_kernel(const __grid
     __syncthreads();
     /* programmatic dependent launch: nothing global before the previous step's writes are visible */
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    const uint32_t tl_slot = blockIdx.x * WARPS + warp;
+    timeline_mark(TL, tl_slot, 0);
 
     if (tid == 0) { /* all sources -> shared memory; bulk copies of at most 32 KB each */
         const uint32_t xy_bytes = p.src_packs_pad * 32u, gm_bytes = p.src_packs_pad * 16u;
@@ -105,6 +119,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_world_kernel(const __grid
     }
 
     mbar_wait(bar, 0);
+    timeline_mark(TL, tl_slot, 1);
 
     for (uint32_t s = warp; s < p.nslab; s += WARPS) {
         const uint32_t pk0 = s * p.slab_packs;
@@ -133,6 +148,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_world_kernel(const __grid
 
     /* pair loop done: the next step's grid may be scheduled into the slots that free up from here on */
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    timeline_mark(TL, tl_slot, 2);
     __syncthreads();
 
     if (tid < (uint32_t)TILE && my_i < p.total_len) {
@@ -144,6 +160,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_world_kernel(const __grid
         }
         integrate_store_vx(p, my_i, sum, my_v, my_x);
     }
+    timeline_mark(TL, tl_slot, 3);
 }
 
 }  // namespace nb

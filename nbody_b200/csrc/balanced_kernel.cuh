@@ -12,17 +12,20 @@
  *
  *   - all sources are staged in shared memory once per CTA (TMA bulk copies, as in small_kernel.cuh); the targets of
  *     the rows a CTA touches (pos, vel, radius) are staged beside them at kernel entry, off the critical path;
- *   - the warps take units from a queue of the CTA's range (a shared-memory counter), compute them with the same
- *     pair arithmetic and the same even/odd chains as the other kernels (interact_pack) and leave each unit's
- *     even + odd sum in shared memory;
- *   - no barrier after the pair loop: the warp that completes the last of the CTA's units of a row (a shared-memory
- *     counter per row) finishes that row at once.  A row whose nslab units all belong to this CTA is added up in
- *     slab order from shared memory and integrated.  A row that straddles a CTA boundary (at most two per CTA) goes
- *     through the global partial buffer and an arrival ticket exactly like step_kernel.cuh -- this CTA's slab sums
- *     are stored, and the last of the row's CTAs to arrive adds ALL nslab partials in slab order and integrates.
- *     The units of those rows are first in the queue, so that chain of L2 round trips (store, ticket,
- *     ceil(nslab / 16) rounds of loads: 3 ... 5 us at the end of the first version of this kernel) runs while the
- *     other warps are still in their pair loops.
+ *   - the CTA's range is cut into WARPS contiguous runs, one per warp.  A warp walks its run with the same pair
+ *     arithmetic and the same even/odd chains as the other kernels (interact_pack); consecutive slabs of a row go
+ *     back to back with the targets in registers, so a unit boundary costs a slab-sum store and nothing else, and
+ *     slabs can be short (the plan picks ~10 units per warp: the run lengths differ by at most one unit);
+ *   - after one __syncthreads one warp per row finishes it: a row whose nslab units all belong to this CTA is added
+ *     up in slab order from shared memory and integrated; a row that straddles a CTA boundary (at most two per CTA)
+ *     goes through the global partial buffer and an arrival ticket exactly like step_kernel.cuh -- this CTA's slab
+ *     sums are stored, and the last of the row's CTAs to arrive adds ALL nslab partials in slab order and integrates.
+ *
+ * Two earlier versions are on record (profiles/r02_balanced_v1_sweep.txt, r02_balanced_v2_modes.txt,
+ * r02_step_timelines_v2.txt): units handed out one at a time -- round-robin, or from a shared-memory queue with
+ * per-row completion counters and no barrier -- paid ~2 600 clk per unit at the unit boundaries (all warps of an SM
+ * reach them together, so nobody hides the target fetch, the index arithmetic, the fence and the atomics) and lost
+ * to the shipped plans at most sizes.
  *
  * The summation order is the plan's alone (slab boundaries, even/odd chains, slabs in order): which CTA computed
  * which unit does not enter, so the results are bit-identical to step_kernel.cuh and small_kernel.cuh with the same
@@ -51,12 +54,11 @@ __host__ __device__ inline BalancedGeom balanced_geom(uint32_t rows, uint32_t ns
 }
 
 /* dynamic shared memory: sources [src_packs_pad] x 48 B | unit sums [upc_max][32 T] float2 |
- * staged targets [rpc_max][32 T] x (pos, vel: float2; radius: float) | row counters [rpc_max] | mbarrier | queue */
+ * staged targets [rpc_max][32 T] x (pos, vel: float2; radius: float) | mbarrier */
 __host__ __device__ inline size_t balanced_smem_bytes(uint32_t src_packs_pad, uint32_t nslab, int T, uint32_t rows,
                                                       uint32_t ctas) {
     const BalancedGeom g = balanced_geom(rows, nslab, ctas);
-    return (size_t)src_packs_pad * 48 + (size_t)g.upc_max * 32 * T * sizeof(float2) + (size_t)g.rpc_max * 32 * T * 20 +
-           (size_t)((g.rpc_max + 1u) & ~1u) * sizeof(unsigned) + 16;
+    return (size_t)src_packs_pad * 48 + (size_t)g.upc_max * 32 * T * sizeof(float2) + (size_t)g.rpc_max * 32 * T * 20 + 16;
 }
 
 /* integrate_store_vx with every field of the parameter block already in registers (RowOut).  Inside the out-of-line
@@ -178,8 +180,7 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
 }
 
 /* StepParams as the other kernels see it; fold_tiles carries the number of target rows of this launch. */
-/* MODE: experiment switches (bit 0: units by warp number in rounds instead of the queue; bit 1: natural unit order;
- * bit 2: whole rows finished after a CTA barrier, one warp per row; bit 3: record the timeline) */
+/* MODE bit 3: record the per-warp timeline (tools/step_timeline.py). */
 template <int WARPS, int T, int UNR, int MODE = 0>
 __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_constant__ StepParams p) {
     constexpr int ROW = 32 * T;
@@ -193,9 +194,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     float2 *s_tpos = s_part + (size_t)geo.upc_max * ROW;                  /* [rpc_max][ROW]     */
     float2 *s_tvel = s_tpos + (size_t)geo.rpc_max * ROW;
     float *s_trad = reinterpret_cast<float *>(s_tvel + (size_t)geo.rpc_max * ROW);
-    unsigned *s_rowcnt = reinterpret_cast<unsigned *>(s_trad + (size_t)geo.rpc_max * ROW); /* [rpc_max] units done per row */
-    uint64_t *bar = reinterpret_cast<uint64_t *>(s_rowcnt + ((geo.rpc_max + 1u) & ~1u));
-    unsigned *s_next = reinterpret_cast<unsigned *>(bar + 1);             /* the CTA's unit queue */
+    uint64_t *bar = reinterpret_cast<uint64_t *>(s_trad + (size_t)geo.rpc_max * ROW);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     /* this CTA's units, and the rows (launch-local numbers) they belong to */
@@ -204,22 +203,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     const uint32_t L = u1 - u0;
     const uint32_t row_first = u0 / p.nslab;
     const uint32_t nrow = (u1 - 1) / p.nslab - row_first + 1;
-    /* Queue order: the units of the rows this CTA shares with a neighbour come first -- the head of the range when
-     * it starts inside a row, then the tail when it ends inside one -- so that their slab sums are published, and
-     * the row finished by whichever CTA comes last, while the rest of the pair loop is still running. */
-    const uint32_t head_end = min((row_first + 1) * p.nslab, u1) - u0;   /* units of the first row       */
-    const bool head_split = head_end < p.nslab;                           /* ... which is not whole here  */
-    const uint32_t n_head = (head_split && !(MODE & 2)) ? head_end : 0u;
-    const uint32_t tail_begin = max(((u1 - 1) / p.nslab) * p.nslab, u0) - u0;
-    const bool tail_split = nrow > 1 && (L - tail_begin) < p.nslab;
-    const uint32_t n_tail = (tail_split && !(MODE & 2)) ? L - tail_begin : 0u;
 
     if (tid == 0) {
         mbar_init(bar, 1);
-        *s_next = WARPS; /* the first WARPS queue entries are taken by warp number */
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (uint32_t k = tid; k < nrow; k += WARPS * 32) s_rowcnt[k] = 0;
     __syncthreads();
     /* programmatic dependent launch: nothing global before the previous step's writes are visible */
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -256,24 +244,29 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     __syncthreads();
     mbar_wait(bar, 0);
     timeline_mark(TL, tl_slot, 1);
-    timeline_mark(TL, tl_slot, 2); /* warps without a unit */
 
-    for (uint32_t q = warp; q < L;) {
-        /* queue entry -> unit of the range: head units, tail units, then the middle */
-        const uint32_t ul = q < n_head ? q : q < n_head + n_tail ? tail_begin + (q - n_head) : q - n_tail;
-        const uint32_t u = u0 + ul;
-        const uint32_t row = u / p.nslab, s = u - row * p.nslab;
-        const uint32_t rc = row - row_first;
-        const uint32_t t = rc * ROW + lane;
-        {
-            float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
+    /* Warp w walks the contiguous run [w L / WARPS, (w + 1) L / WARPS) of the CTA's units: consecutive slabs of a row
+     * back to back with the targets in registers -- between two units only the slab sum is stored and the chains
+     * restart -- and a fresh set of targets where the run crosses into the next row. */
+    {
+        const uint32_t a = (uint32_t)((uint64_t)warp * L / WARPS), b = (uint32_t)((uint64_t)(warp + 1) * L / WARPS);
+        uint32_t row = (u0 + a) / p.nslab, s = (u0 + a) - row * p.nslab;
+        float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
+        bool fresh = true;
+        for (uint32_t ul = a; ul < b; ul++) {
+            if (fresh) {
+                const uint32_t t = (row - row_first) * ROW + lane;
+#pragma unroll
+                for (int k = 0; k < T; k++) {
+                    const float2 x = s_tpos[t + k * 32];
+                    const float r = s_trad[t + k * 32];
+                    ntx[k] = make_float2(-x.x, -x.x);
+                    nty[k] = make_float2(-x.y, -x.y);
+                    rho[k] = make_float2(r, r);
+                }
+            }
 #pragma unroll
             for (int k = 0; k < T; k++) {
-                const float2 x = s_tpos[t + k * 32];
-                const float r = s_trad[t + k * 32];
-                ntx[k] = make_float2(-x.x, -x.x);
-                nty[k] = make_float2(-x.y, -x.y);
-                rho[k] = make_float2(r, r);
                 ax[k] = make_float2(0.f, 0.f);
                 ay[k] = make_float2(0.f, 0.f);
             }
@@ -293,43 +286,26 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
             for (int k = 0; k < T; k++)
                 s_part[(size_t)ul * ROW + k * 32 + lane] =
                     make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+            fresh = ++s == p.nslab;
+            if (fresh) {
+                s = 0;
+                row++;
+            }
         }
-
-        /* the warp that completes the last of this CTA's units of a row finishes the row; everyone takes the next
-         * queue entry */
-        const uint32_t ub = row * p.nslab;                       /* the row's unit of slab 0           */
-        const uint32_t s_lo = ub >= u0 ? 0u : u0 - ub;           /* this CTA holds slabs [s_lo, s_hi)  */
-        const uint32_t s_hi = min(p.nslab, u1 - ub);
-        __syncwarp();
-        unsigned done = 0, qn = 0;
-        if (lane == 0) {
-            __threadfence_block();
-            done = atomicAdd(&s_rowcnt[rc], 1u) + 1u == s_hi - s_lo;
-            if (!(MODE & 1)) qn = atomicAdd(s_next, 1u);
-        }
-        done = __shfl_sync(0xffffffffu, done, 0);
-        timeline_mark(TL, tl_slot, 2);
-        if (MODE & 1) q += WARPS;
-        else q = __shfl_sync(0xffffffffu, qn, 0);
-        if ((MODE & 4) && s_lo == 0 && s_hi == p.nslab) continue;
-        if (!done) continue;
-        __threadfence_block();
-
-        balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row, u0, u1, G, geo.units, lane);
     }
+    timeline_mark(TL, tl_slot, 2);
 
-    /* this thread's pair loops are done: once every thread is here the next step's grid may be scheduled */
+    /* pair loop done: the next step's grid may be scheduled into the slots that free up from here on */
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (!(MODE & 4)) timeline_mark(TL, tl_slot, 3);
-    if (MODE & 4) {
-        __syncthreads();
-        for (uint32_t rc = warp; rc < nrow; rc += WARPS) {
-            const uint32_t row = row_first + rc, ub = row * p.nslab;
-            if (ub >= u0 && ub + p.nslab <= u1)
-                balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row, u0, u1, G, geo.units, lane);
-        }
-        timeline_mark(TL, tl_slot, 3);
+    __syncthreads();
+
+    /* finish the rows, one warp per row; the rows shared with a neighbour CTA (the first and the last of the range)
+     * go first: theirs is the longer chain (stores, ticket, partial loads) */
+    for (uint32_t k = warp; k < nrow; k += WARPS) {
+        const uint32_t rc = k == 0 ? 0u : k == 1 ? nrow - 1 : k - 1;
+        balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row_first + rc, u0, u1, G, geo.units, lane);
     }
+    timeline_mark(TL, tl_slot, 3);
 }
 
 }  // namespace nb

@@ -226,14 +226,8 @@ static const Variant kVariants[] = {
     NB_VARIANT_BALANCED("b16x4", 16, 4, 2, 0),
     NB_VARIANT_BALANCED("b8x4", 8, 4, 2, 0),
     NB_VARIANT_BALANCED("b32x2", 32, 2, 2, 0),
-    NB_VARIANT_BALANCED("b16x2m1", 16, 2, 2, 1),
-    NB_VARIANT_BALANCED("b16x2m2", 16, 2, 2, 2),
-    NB_VARIANT_BALANCED("b16x2m4", 16, 2, 2, 4),
-    NB_VARIANT_BALANCED("b16x2m7", 16, 2, 2, 7),
-    NB_VARIANT_BALANCED("b16x4m7", 16, 4, 2, 7),
     NB_VARIANT_BALANCED("b16x2t", 16, 2, 2, 8),   /* with the per-warp timeline (tools/step_timeline.py) */
-    NB_VARIANT_BALANCED("b16x2m7t", 16, 2, 2, 15),
-    NB_VARIANT_BALANCED("b16x2m2t", 16, 2, 2, 10),
+    NB_VARIANT_BALANCED("b16x4t", 16, 4, 2, 8),
     /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
      * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
     NB_VARIANT_EXACT("ref8", 8),
@@ -455,10 +449,13 @@ static void choose_slabs_small(Plan &pl, uint32_t forced_slab_len) {
     pl.nslab = ceil_div(pl.src_packs, pl.slab_packs);
 }
 
-/* Slabs of a mid-size World (balanced_kernel.cuh): every CTA gets ceil(rows * nslab / CTAs) units at most and its
- * warps walk them in rounds, so the slab count decides how full the last round is.  Slabs of 128 ... 512 sources
- * (chains of 64 ... 256 terms); cost of a plan = rounds x (slab length + a fixed cost per unit). */
-static const double kBalancedUnitFixedPacks = 3.0; /* per unit, in packs of work: target fetch, index arithmetic, sum store */
+/* Slabs of a mid-size World (balanced_kernel.cuh): a CTA gets at most ceil(rows * nslab / CTAs) units and cuts them
+ * into WARPS contiguous runs, so a warp walks ceil(that / WARPS) units at most: the step takes as long as the longest
+ * run.  A unit boundary inside a run costs next to nothing (a slab-sum store), so slabs are SHORT -- ten or more units
+ * per warp, runs that differ by one unit in ten -- down to 32 sources, as far as the unit sums fit in shared memory
+ * beside the sources.  Shorter chains only help the accuracy.  Cost of a plan = longest run x (slab + fixed). */
+static const double kBalancedUnitFixedPacks = 0.5; /* per unit, in packs of work: slab-sum store, chain restart */
+static const size_t kBalancedMaxSmem = 220u << 10;
 static void choose_slabs_balanced(Plan &pl, int sm_count, uint32_t forced_slab_len) {
     const uint32_t unr = 4;
     const uint32_t warps = (uint32_t)pl.var->threads / 32;
@@ -471,18 +468,20 @@ static void choose_slabs_balanced(Plan &pl, int sm_count, uint32_t forced_slab_l
     if (forced_slab_len) {
         pl.slab_packs = std::max(unr, ceil_div(ceil_div(forced_slab_len, 4), unr) * unr);
     } else {
+        /* the shortest slabs within 1 % of the cheapest plan */
         double best = 1e300;
-        uint32_t best_sp = 32;
-        const uint32_t n_lo = std::max(1u, ceil_div(pl.src_packs, 128u)), n_hi = std::max(n_lo, pl.src_packs / 32u);
-        for (uint32_t n = n_lo; n <= n_hi; n++) {
-            const uint32_t sp = ceil_div(ceil_div(pl.src_packs, n), unr) * unr;
-            if (ceil_div(pl.src_packs, sp) != n) continue;
-            const uint32_t units = pl.ntiles * n, ctas = std::min<uint32_t>((uint32_t)sm_count, units);
-            const uint32_t rounds = ceil_div(ceil_div(units, ctas), warps);
-            const double cost = rounds * ((double)sp + kBalancedUnitFixedPacks);
-            if (cost < best * 0.999) {
-                best = cost;
-                best_sp = sp;
+        uint32_t best_sp = 128;
+        const uint32_t n_lo = std::max(1u, ceil_div(pl.src_packs, 128u)), n_hi = std::max(n_lo, pl.src_packs / 8u);
+        for (int pass = 0; pass < 2; pass++) {
+            for (uint32_t n = n_lo; n <= n_hi; n++) {
+                const uint32_t sp = ceil_div(ceil_div(pl.src_packs, n), unr) * unr;
+                if (ceil_div(pl.src_packs, sp) != n) continue;
+                const uint32_t units = pl.ntiles * n, ctas = std::min<uint32_t>((uint32_t)sm_count, units);
+                if (n > n_lo && balanced_smem_bytes(pl.src_packs_pad, n, pl.var->T, pl.ntiles, ctas) > kBalancedMaxSmem) break;
+                const uint32_t run = ceil_div(ceil_div(units, ctas), warps);
+                const double cost = run * ((double)sp + kBalancedUnitFixedPacks);
+                if (pass == 0) best = std::min(best, cost);
+                else if (cost <= best * 1.01) best_sp = sp;
             }
         }
         pl.slab_packs = best_sp;
@@ -533,7 +532,6 @@ static const Variant *find_variant(const char *name) {
  * NBODY_SMALL_MAX_N caps N (0: never use the small-World kernel).
  */
 static const size_t kSmallWorldMaxSmem = 200u << 10;
-static const size_t kBalancedMaxSmem = 220u << 10;
 static const double kSmallWorldMinUtil = 0.78; /* T >= 3: CTAs / SMs */
 static const Variant *small_variant_for(uint32_t N, int sm_count) {
     const char *e = getenv("NBODY_SMALL_MAX_N");

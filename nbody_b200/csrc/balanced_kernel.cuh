@@ -7,29 +7,40 @@
  * machine: N = 16 384 is 512 warps of targets for 148 SMs.  The small-World kernel runs it as 128 CTAs (20 SMs idle,
  * 47.7 us), the (tile, slab) kernel as 1 024 CTAs on 888 slots (1.15 waves, 48.3 us); the arithmetic alone is 38 us.
  * N = 10 000: 22.5 us for 14 us of arithmetic.  Here the work is cut into units of one target ROW (32 T targets, T
- * per lane) against one SLAB of sources, rows x nslab units in row-major order, and CTA c of G = min(SMs, units)
- * takes the contiguous unit range [c U / G, (c + 1) U / G): no SM gets more than one unit above the average.
+ * per lane) against one SLAB of sources, and shared out over G = min(SMs, units) CTAs like this:
  *
- *   - all sources are staged in shared memory once per CTA (TMA bulk copies, as in small_kernel.cuh); the targets of
- *     the rows a CTA touches (pos, vel, radius) are staged beside them at kernel entry, off the critical path;
- *   - the CTA's range is cut into WARPS contiguous runs, one per warp.  A warp walks its run with the same pair
- *     arithmetic and the same even/odd chains as the other kernels (interact_pack); consecutive slabs of a row go
- *     back to back with the targets in registers, so a unit boundary costs a slab-sum store and nothing else, and
- *     slabs can be short (the plan picks ~10 units per warp: the run lengths differ by at most one unit);
- *   - after one __syncthreads one warp per row finishes it: a row whose nslab units all belong to this CTA is added
- *     up in slab order from shared memory and integrated; a row that straddles a CTA boundary (at most two per CTA)
- *     goes through the global partial buffer and an arrival ticket exactly like step_kernel.cuh -- this CTA's slab
- *     sums are stored, and the last of the row's CTAs to arrive adds ALL nslab partials in slab order and integrates.
+ *   - every CTA gets w = floor(rows / G) WHOLE rows (all nslab units of each);
+ *   - the r = rows - w G rows left over are SHARED: their r nslab units, in row-major order, are cut into G equal
+ *     contiguous pieces, one per CTA (less than one row's worth each).
  *
- * Two earlier versions are on record (profiles/r02_balanced_v1_sweep.txt, r02_balanced_v2_modes.txt,
- * r02_step_timelines_v2.txt): units handed out one at a time -- round-robin, or from a shared-memory queue with
- * per-row completion counters and no barrier -- paid ~2 600 clk per unit at the unit boundaries (all warps of an SM
- * reach them together, so nobody hides the target fetch, the index arithmetic, the fence and the atomics) and lost
- * to the shipped plans at most sizes.
+ * So every CTA has the same number of units to within one.  Inside the CTA
  *
- * The summation order is the plan's alone (slab boundaries, even/odd chains, slabs in order): which CTA computed
- * which unit does not enter, so the results are bit-identical to step_kernel.cuh and small_kernel.cuh with the same
- * slab length, for any launch range and any number of GPUs (tests/test_gpu_parity.py).
+ *   - all sources are staged in shared memory once (TMA bulk copies, as in small_kernel.cuh); the targets of the rows
+ *     the CTA touches (pos, vel, radius) are staged beside them at kernel entry, off the critical path;
+ *   - the CTA's unit list -- its piece of the shared rows FIRST, then its whole rows -- is cut into CW contiguous
+ *     runs, one per compute warp.  A warp walks its run with the same pair arithmetic and the same even/odd chains as
+ *     the other kernels (interact_pack); consecutive slabs of a row go back to back with the targets in registers, so
+ *     a unit boundary costs a slab-sum store and nothing else, and slabs can be short (runs differ by one unit);
+ *   - one more warp, the FINISHER, computes no pairs.  It sleeps on an mbarrier until the compute warps have left the
+ *     shared part of the list (a few us into the step), then publishes this CTA's slab sums of the shared rows in the
+ *     global partial buffer and takes an arrival ticket per row, exactly like step_kernel.cuh; where it is the last
+ *     of a row's CTAs to arrive it adds ALL nslab partials in slab order and integrates.  That chain of L2 round trips
+ *     (stores, fence, ticket, ceil(nslab / 16) rounds of loads: 3 ... 6 us) runs beside the pair loops of the whole
+ *     rows instead of after them;
+ *   - after one __syncthreads the whole rows are added up in slab order from shared memory and integrated, 32 targets
+ *     per warp, all warps at once.
+ *
+ * The summation order is the plan's alone (slab boundaries, even/odd chains, slabs in order): which CTA or warp
+ * computed which unit does not enter, so the results are bit-identical to step_kernel.cuh and small_kernel.cuh with
+ * the same slab length, for any launch range and any number of GPUs (tests/test_gpu_parity.py).
+ *
+ * Three earlier versions are on record (profiles/r02_balanced_v1_sweep.txt, r02_balanced_v2_modes.txt,
+ * r02_step_timelines_v2.txt, r02_step_timelines_v3.txt, r02_balanced_v3_sweep.txt).  Units handed out one at a time
+ * -- round-robin, or from a shared-memory queue with per-row completion counters -- paid ~2 600 clk per unit at the
+ * unit boundaries: all warps of an SM reach them together, so nobody hides the target fetch, the index arithmetic,
+ * the fence and the atomics.  Contiguous runs fixed that, but with every CTA's range starting and ending inside a row
+ * the ticket chain of those two rows came after the pair loop: 5.7 us of a 48.7 us step at N = 16 384 (T = 2,
+ * 46 slabs), 14 us at T = 4 with 73 slabs.
  */
 #pragma once
 
@@ -39,22 +50,28 @@
 namespace nb {
 
 struct BalancedGeom {
-    uint32_t units;   /* rows x nslab                                        */
-    uint32_t upc_max; /* most units any CTA gets                             */
-    uint32_t rpc_max; /* most rows any CTA touches (whole or partly)         */
+    uint32_t whole;        /* w: whole rows per CTA                                        */
+    uint32_t shared_rows;  /* r: rows whose units are spread over all CTAs                  */
+    uint32_t shared_units; /* r x nslab                                                     */
+    uint32_t spc_max;      /* most shared units any CTA gets                                */
+    uint32_t upc_max;      /* most units any CTA gets: spc_max + w x nslab                  */
+    uint32_t rpc_max;      /* most rows any CTA touches: its shared rows + its whole rows   */
 };
 
-/* ROWS target rows against NSLAB slabs over CTAS CTAs (CTAS <= units) */
+/* ROWS target rows against NSLAB slabs over CTAS CTAs (CTAS <= ROWS x NSLAB) */
 __host__ __device__ inline BalancedGeom balanced_geom(uint32_t rows, uint32_t nslab, uint32_t ctas) {
     BalancedGeom g;
-    g.units = rows * nslab;
-    g.upc_max = (g.units + ctas - 1) / ctas;
-    g.rpc_max = (g.upc_max + nslab - 2) / nslab + 1;
+    g.whole = rows / ctas;
+    g.shared_rows = rows - g.whole * ctas;
+    g.shared_units = g.shared_rows * nslab;
+    g.spc_max = (g.shared_units + ctas - 1) / ctas;
+    g.upc_max = g.spc_max + g.whole * nslab;
+    g.rpc_max = (g.spc_max ? (g.spc_max + nslab - 2) / nslab + 1 : 0) + g.whole;
     return g;
 }
 
 /* dynamic shared memory: sources [src_packs_pad] x 48 B | unit sums [upc_max][32 T] float2 |
- * staged targets [rpc_max][32 T] x (pos, vel: float2; radius: float) | mbarrier */
+ * staged targets [rpc_max][32 T] x (pos, vel: float2; radius: float) | 2 mbarriers */
 __host__ __device__ inline size_t balanced_smem_bytes(uint32_t src_packs_pad, uint32_t nslab, int T, uint32_t rows,
                                                       uint32_t ctas) {
     const BalancedGeom g = balanced_geom(rows, nslab, ctas);
@@ -62,9 +79,9 @@ __host__ __device__ inline size_t balanced_smem_bytes(uint32_t src_packs_pad, ui
 }
 
 /* integrate_store_vx with every field of the parameter block already in registers (RowOut).  Inside the out-of-line
- * balanced_finish_row the block is reached through a generic pointer, and the compiler must assume that each of our
- * stores may have changed it: with the fields read through that pointer where they are used, every store was followed
- * by dependent re-loads of part / part_stride / pos / vel / ... (measured: +4.7 us per step at T = 2, +8.5 us at T = 4). */
+ * finishers the block is reached through a generic pointer, and the compiler must assume that each of our stores may
+ * have changed it: with the fields read through that pointer where they are used, every store was followed by
+ * dependent re-loads of part / part_stride / pos / vel / ... (measured: +4.7 us per step at T = 2, +8.5 us at T = 4). */
 struct RowOut {
     float2 *pos, *vel, *acc;
     float *dst0;
@@ -94,81 +111,75 @@ __device__ __forceinline__ void row_integrate_store(const RowOut &o, uint32_t i,
     }
 }
 
-/* Finish one target row (the caller's warp just completed the last of this CTA's units of it): kept out of line so
- * that its registers -- the partial loads of the straddling case -- do not weigh on the pair loop. */
+/*
+ * The finisher's work on one SHARED row: this CTA holds the sums of slabs [s_lo, s_hi) of it (MINE points at the sum
+ * of slab s_lo; consecutive slabs are 32 T float2 apart).  Out of line, so that its registers -- the partial loads
+ * -- do not weigh on the pair loop.  CONTRIBUTORS CTAs hold units of the row.
+ */
 template <int T>
-__device__ __noinline__ void balanced_finish_row(const StepParams &p, const float2 *s_part, const float2 *row_vel,
-                                                 const float2 *row_pos, uint32_t row, uint32_t u0, uint32_t u1, uint32_t G,
-                                                 uint32_t units, uint32_t lane) {
+__device__ __noinline__ void balanced_finish_shared_row(const StepParams &p, const float2 *mine, const float2 *row_vel,
+                                                        const float2 *row_pos, uint32_t tile, uint32_t s_lo, uint32_t s_hi,
+                                                        uint32_t contributors, uint32_t lane) {
     constexpr int ROW = 32 * T;
     /* the parameter block, once */
     const RowOut out = {p.pos, p.vel, p.acc, p.dst_xy[0], p.dst_xy, p.ndst, p.total_len, p.mass_len, p.dt};
     float2 *const part = p.part;
     unsigned *const tile_cnt = p.tile_cnt;
     const uint32_t nslab = p.nslab, part_stride = p.part_stride;
-    const uint32_t ub = row * nslab;                         /* the row's unit of slab 0           */
-    const uint32_t s_lo = ub >= u0 ? 0u : u0 - ub;           /* this CTA holds slabs [s_lo, s_hi)  */
-    const uint32_t s_hi = min(nslab, u1 - ub);
-    const uint32_t tile = p.tile_first + row;
     const uint32_t i0 = tile * ROW + lane;
-    /* this CTA's sum of slab s (s_lo <= s < s_hi) of the row, target k * 32 + lane */
-    auto mine = [&](uint32_t sl, int k) { return s_part[(size_t)(ub + sl - u0) * ROW + k * 32 + lane]; };
-    if (s_lo == 0 && s_hi == nslab) { /* the whole row is here: slab order, from shared memory */
-#pragma unroll
-        for (int k = 0; k < T; k++) {
-            float2 sum = mine(0, k);
-            for (uint32_t sl = 1; sl < nslab; sl++) {
-                const float2 v = mine(sl, k);
-                sum.x = __fadd_rn(sum.x, v.x);
-                sum.y = __fadd_rn(sum.y, v.y);
-            }
-            const uint32_t i = i0 + k * 32;
-            if (i < out.total_len) row_integrate_store(out, i, sum, row_vel[k * 32 + lane], row_pos[k * 32 + lane]);
-        }
-        return;
-    }
-    /* the row straddles a CTA boundary: publish this CTA's slab sums, take a ticket */
-    for (uint32_t sl = s_lo; sl < s_hi; sl++) {
-#pragma unroll
-        for (int k = 0; k < T; k++) __stcg(&part[(size_t)sl * part_stride + i0 + k * 32], mine(sl, k));
-    }
-    __threadfence();
-    __syncwarp();
-    int last = 0;
-    if (lane == 0) {
-        /* unit u belongs to CTA ceil((u + 1) G / U) - 1 */
-        const uint32_t c_first = (uint32_t)((((uint64_t)ub + 1) * G + units - 1) / units) - 1;
-        const uint32_t c_last = (uint32_t)((((uint64_t)ub + nslab) * G + units - 1) / units) - 1;
-        const unsigned ticket = atomicAdd(&tile_cnt[tile], 1u);
-        last = (ticket == c_last - c_first);
-        if (last) tile_cnt[tile] = 0; /* ready for the next step */
-    }
-    last = __shfl_sync(0xffffffffu, last, 0);
-    if (!last) return;
-    __threadfence();
-    /* last CTA of this row: all slab partials in slab order; RB slabs of all T targets in flight together */
-    constexpr int RB = T <= 2 ? 16 : 8;
     float2 sum[T];
-    for (uint32_t s0 = 0; s0 < nslab; s0 += RB) {
-        float2 v[T][RB];
+    if (contributors > 1) {
+        /* publish this CTA's slab sums, take a ticket */
+        for (uint32_t sl = s_lo; sl < s_hi; sl++) {
 #pragma unroll
-        for (int k = 0; k < T; k++) {
-#pragma unroll
-            for (int w = 0; w < RB; w++)
-                if (s0 + w < nslab) v[k][w] = __ldcg(&part[(size_t)(s0 + w) * part_stride + i0 + k * 32]);
+            for (int k = 0; k < T; k++)
+                __stcg(&part[(size_t)sl * part_stride + i0 + k * 32], mine[(size_t)(sl - s_lo) * ROW + k * 32 + lane]);
         }
+        __threadfence();
+        __syncwarp();
+        int last = 0;
+        if (lane == 0) {
+            const unsigned ticket = atomicAdd(&tile_cnt[tile], 1u);
+            last = (ticket == contributors - 1);
+            if (last) tile_cnt[tile] = 0; /* ready for the next step */
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (!last) return;
+        __threadfence();
+        /* last CTA of this row: all slab partials in slab order; RB slabs of all T targets in flight together */
+        constexpr int RB = T <= 2 ? 16 : 8;
+        for (uint32_t s0 = 0; s0 < nslab; s0 += RB) {
+            float2 v[T][RB];
 #pragma unroll
-        for (int k = 0; k < T; k++) {
+            for (int k = 0; k < T; k++) {
 #pragma unroll
-            for (int w = 0; w < RB; w++) {
-                if (s0 + w < nslab) {
-                    if (s0 + w == 0) {
-                        sum[k] = v[k][0];
-                    } else {
-                        sum[k].x = __fadd_rn(sum[k].x, v[k][w].x);
-                        sum[k].y = __fadd_rn(sum[k].y, v[k][w].y);
+                for (int w = 0; w < RB; w++)
+                    if (s0 + w < nslab) v[k][w] = __ldcg(&part[(size_t)(s0 + w) * part_stride + i0 + k * 32]);
+            }
+#pragma unroll
+            for (int k = 0; k < T; k++) {
+#pragma unroll
+                for (int w = 0; w < RB; w++) {
+                    if (s0 + w < nslab) {
+                        if (s0 + w == 0) {
+                            sum[k] = v[k][0];
+                        } else {
+                            sum[k].x = __fadd_rn(sum[k].x, v[k][w].x);
+                            sum[k].y = __fadd_rn(sum[k].y, v[k][w].y);
+                        }
                     }
                 }
+            }
+        }
+    } else { /* the whole row happens to be in this CTA's piece */
+#pragma unroll
+        for (int k = 0; k < T; k++) sum[k] = mine[k * 32 + lane];
+        for (uint32_t sl = 1; sl < nslab; sl++) {
+#pragma unroll
+            for (int k = 0; k < T; k++) {
+                const float2 v = mine[(size_t)sl * ROW + k * 32 + lane];
+                sum[k].x = __fadd_rn(sum[k].x, v.x);
+                sum[k].y = __fadd_rn(sum[k].y, v.y);
             }
         }
     }
@@ -179,12 +190,40 @@ __device__ __noinline__ void balanced_finish_row(const StepParams &p, const floa
     }
 }
 
-/* StepParams as the other kernels see it; fold_tiles carries the number of target rows of this launch. */
-/* MODE bit 3: record the per-warp timeline (tools/step_timeline.py). */
-template <int WARPS, int T, int UNR, int MODE = 0>
-__global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_constant__ StepParams p) {
+/* One target of a WHOLE row: slab sums MINE[s * stride] for s < nslab, in slab order, then the integrator. */
+__device__ __noinline__ void balanced_finish_whole(const StepParams &p, const float2 *mine, uint32_t stride, float2 v0,
+                                                   float2 x0, uint32_t i) {
+    const RowOut out = {p.pos, p.vel, p.acc, p.dst_xy[0], p.dst_xy, p.ndst, p.total_len, p.mass_len, p.dt};
+    const uint32_t nslab = p.nslab;
+    float2 sum = mine[0];
+    uint32_t sl = 1;
+    for (; sl + 8 <= nslab; sl += 8) {
+        float2 v[8];
+#pragma unroll
+        for (int w = 0; w < 8; w++) v[w] = mine[(size_t)(sl + w) * stride];
+#pragma unroll
+        for (int w = 0; w < 8; w++) {
+            sum.x = __fadd_rn(sum.x, v[w].x);
+            sum.y = __fadd_rn(sum.y, v[w].y);
+        }
+    }
+    for (; sl < nslab; sl++) {
+        const float2 v = mine[(size_t)sl * stride];
+        sum.x = __fadd_rn(sum.x, v.x);
+        sum.y = __fadd_rn(sum.y, v.y);
+    }
+    if (i < out.total_len) row_integrate_store(out, i, sum, v0, x0);
+}
+
+/*
+ * CW compute warps + 1 finisher warp.  StepParams as the other kernels see it; fold_tiles carries the number of target
+ * rows of this launch.  TL: record the per-warp timeline (tools/step_timeline.py).
+ */
+template <int CW, int T, int UNR, bool TL = false>
+__global__ void __launch_bounds__((CW + 1) * 32, 1) balanced_kernel(const __grid_constant__ StepParams p) {
     constexpr int ROW = 32 * T;
-    const uint32_t G = gridDim.x;
+    constexpr int THREADS = (CW + 1) * 32;
+    const uint32_t G = gridDim.x, c = blockIdx.x;
     const BalancedGeom geo = balanced_geom(p.fold_tiles, p.nslab, G);
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -194,42 +233,52 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
     float2 *s_tpos = s_part + (size_t)geo.upc_max * ROW;                  /* [rpc_max][ROW]     */
     float2 *s_tvel = s_tpos + (size_t)geo.rpc_max * ROW;
     float *s_trad = reinterpret_cast<float *>(s_tvel + (size_t)geo.rpc_max * ROW);
-    uint64_t *bar = reinterpret_cast<uint64_t *>(s_trad + (size_t)geo.rpc_max * ROW);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(s_trad + (size_t)geo.rpc_max * ROW); /* [0] sources, [1] shared part done */
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    /* this CTA's units, and the rows (launch-local numbers) they belong to */
-    const uint32_t u0 = (uint32_t)((uint64_t)blockIdx.x * geo.units / G);
-    const uint32_t u1 = (uint32_t)((uint64_t)(blockIdx.x + 1) * geo.units / G);
-    const uint32_t L = u1 - u0;
-    const uint32_t row_first = u0 / p.nslab;
-    const uint32_t nrow = (u1 - 1) / p.nslab - row_first + 1;
+    /* this CTA's piece [us0, us1) of the shared units and the shared rows (numbered from 0) it lies in */
+    const uint32_t us0 = (uint32_t)((uint64_t)c * geo.shared_units / G);
+    const uint32_t us1 = (uint32_t)((uint64_t)(c + 1) * geo.shared_units / G);
+    const uint32_t Ls = us1 - us0;
+    const uint32_t srow_first = Ls ? us0 / p.nslab : 0u;
+    const uint32_t nsr = Ls ? (us1 - 1) / p.nslab - srow_first + 1 : 0u;
+    const uint32_t L = Ls + geo.whole * p.nslab;   /* the unit list: shared piece, then whole rows */
+    const uint32_t nrow = nsr + geo.whole;         /* staged rows: shared rows, then whole rows    */
+    /* launch-local row number of staged row j */
+    auto row_of = [&](uint32_t j) { return j < nsr ? geo.whole * G + srow_first + j : c * geo.whole + (j - nsr); };
+    /* compute warps whose run begins inside the shared piece: they tell the finisher when they have left it */
+    uint32_t leavers = 0;
+    for (uint32_t w = 0; w < (uint32_t)CW; w++) {
+        const uint32_t wa = (uint32_t)((uint64_t)w * L / CW), wb = (uint32_t)((uint64_t)(w + 1) * L / CW);
+        leavers += wa < Ls && wb > wa;
+    }
 
     if (tid == 0) {
-        mbar_init(bar, 1);
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], leavers ? leavers : 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     /* programmatic dependent launch: nothing global before the previous step's writes are visible */
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    constexpr bool TL = (MODE & 8) != 0;
-    const uint32_t tl_slot = blockIdx.x * WARPS + warp;
+    const uint32_t tl_slot = c * (CW + 1) + warp;
     timeline_mark(TL, tl_slot, 0);
 
     if (tid == 0) { /* all sources -> shared memory; bulk copies of at most 32 KB each */
         const uint32_t xy_bytes = p.src_packs_pad * 32u, gm_bytes = p.src_packs_pad * 16u;
-        mbar_expect_tx(bar, xy_bytes + gm_bytes);
+        mbar_expect_tx(&bar[0], xy_bytes + gm_bytes);
         for (uint32_t o = 0; o < xy_bytes; o += 32768u)
             bulk_g2s(reinterpret_cast<unsigned char *>(s_xy) + o, reinterpret_cast<const unsigned char *>(p.src_xy) + o,
-                     min(32768u, xy_bytes - o), bar);
+                     min(32768u, xy_bytes - o), &bar[0]);
         for (uint32_t o = 0; o < gm_bytes; o += 32768u)
             bulk_g2s(reinterpret_cast<unsigned char *>(s_gm) + o, reinterpret_cast<const unsigned char *>(p.src_gm) + o,
-                     min(32768u, gm_bytes - o), bar);
+                     min(32768u, gm_bytes - o), &bar[0]);
     }
 
     /* the targets of every row this CTA touches: one round trip, concurrent with the source copy */
-    const uint32_t i_first = (p.tile_first + row_first) * ROW;
-    for (uint32_t k = tid; k < nrow * ROW; k += WARPS * 32) {
-        const uint32_t i = i_first + k;
+    for (uint32_t k = tid; k < nrow * ROW; k += THREADS) {
+        const uint32_t j = k / ROW;
+        const uint32_t i = (p.tile_first + row_of(j)) * ROW + (k - j * ROW);
         float2 x = make_float2(0.f, 0.f), v = make_float2(0.f, 0.f);
         float r = 1.f;
         if (i < p.total_len) {
@@ -242,20 +291,25 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
         s_trad[k] = r;
     }
     __syncthreads();
-    mbar_wait(bar, 0);
-    timeline_mark(TL, tl_slot, 1);
 
-    /* Warp w walks the contiguous run [w L / WARPS, (w + 1) L / WARPS) of the CTA's units: consecutive slabs of a row
-     * back to back with the targets in registers -- between two units only the slab sum is stored and the chains
-     * restart -- and a fresh set of targets where the run crosses into the next row. */
-    {
-        const uint32_t a = (uint32_t)((uint64_t)warp * L / WARPS), b = (uint32_t)((uint64_t)(warp + 1) * L / WARPS);
-        uint32_t row = (u0 + a) / p.nslab, s = (u0 + a) - row * p.nslab;
+    if (warp < (uint32_t)CW) {
+        mbar_wait(&bar[0], 0);
+        timeline_mark(TL, tl_slot, 1);
+        /* Compute warp w walks the contiguous run [w L / CW, (w + 1) L / CW) of the unit list. */
+        const uint32_t a = (uint32_t)((uint64_t)warp * L / CW), b = (uint32_t)((uint64_t)(warp + 1) * L / CW);
+        uint32_t j = 0, s = 0; /* staged row and slab of unit a */
+        if (a < Ls) {
+            j = (us0 + a) / p.nslab - srow_first;
+            s = (us0 + a) - (srow_first + j) * p.nslab;
+        } else {
+            j = nsr + (a - Ls) / p.nslab;
+            s = (a - Ls) - (j - nsr) * p.nslab;
+        }
         float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
         bool fresh = true;
         for (uint32_t ul = a; ul < b; ul++) {
             if (fresh) {
-                const uint32_t t = (row - row_first) * ROW + lane;
+                const uint32_t t = j * ROW + lane;
 #pragma unroll
                 for (int k = 0; k < T; k++) {
                     const float2 x = s_tpos[t + k * 32];
@@ -286,24 +340,51 @@ __global__ void __launch_bounds__(WARPS * 32, 1) balanced_kernel(const __grid_co
             for (int k = 0; k < T; k++)
                 s_part[(size_t)ul * ROW + k * 32 + lane] =
                     make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+            /* next unit: the next slab of this row, the next row, or -- leaving the shared piece -- the first whole row */
             fresh = ++s == p.nslab;
             if (fresh) {
                 s = 0;
-                row++;
+                j++;
+            }
+            if (ul + 1 == Ls) {
+                fresh = true;
+                s = 0;
+                j = nsr;
+            }
+            if (ul + 1 == Ls || (ul + 1 == b && b < Ls)) { /* this warp's last shared unit is done: tell the finisher */
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar[1]);
             }
         }
+        timeline_mark(TL, tl_slot, 2);
+    } else if (Ls) {
+        /* The finisher: once the shared piece is computed, publish it and finish the rows this CTA arrives last at. */
+        mbar_wait(&bar[1], 0);
+        timeline_mark(TL, tl_slot, 1);
+        for (uint32_t j = 0; j < nsr; j++) {
+            const uint32_t ub = (srow_first + j) * p.nslab;          /* the row's unit of slab 0, in shared units */
+            const uint32_t s_lo = ub >= us0 ? 0u : us0 - ub;         /* this CTA holds slabs [s_lo, s_hi)         */
+            const uint32_t s_hi = min(p.nslab, us1 - ub);
+            /* unit u of the shared units belongs to CTA ceil((u + 1) G / U) - 1 */
+            const uint32_t c_first = (uint32_t)((((uint64_t)ub + 1) * G + geo.shared_units - 1) / geo.shared_units) - 1;
+            const uint32_t c_last = (uint32_t)((((uint64_t)ub + p.nslab) * G + geo.shared_units - 1) / geo.shared_units) - 1;
+            balanced_finish_shared_row<T>(p, s_part + (size_t)(ub + s_lo - us0) * ROW, s_tvel + j * ROW, s_tpos + j * ROW,
+                                          p.tile_first + row_of(j), s_lo, s_hi, c_last - c_first + 1, lane);
+        }
+        timeline_mark(TL, tl_slot, 2);
     }
-    timeline_mark(TL, tl_slot, 2);
 
-    /* pair loop done: the next step's grid may be scheduled into the slots that free up from here on */
+    /* pair loops done: the next step's grid may be scheduled into the slots that free up from here on */
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();
 
-    /* finish the rows, one warp per row; the rows shared with a neighbour CTA (the first and the last of the range)
-     * go first: theirs is the longer chain (stores, ticket, partial loads) */
-    for (uint32_t k = warp; k < nrow; k += WARPS) {
-        const uint32_t rc = k == 0 ? 0u : k == 1 ? nrow - 1 : k - 1;
-        balanced_finish_row<T>(p, s_part, s_tvel + rc * ROW, s_tpos + rc * ROW, row_first + rc, u0, u1, G, geo.units, lane);
+    /* the whole rows: 32 targets per warp, all warps at once */
+    for (uint32_t item = warp; item < geo.whole * T; item += CW + 1) {
+        const uint32_t wr = item / T, k = item - wr * T;
+        const uint32_t j = nsr + wr;
+        const uint32_t t = j * ROW + k * 32 + lane;
+        balanced_finish_whole(p, s_part + (size_t)(Ls + wr * p.nslab) * ROW + k * 32 + lane, ROW, s_tvel[t], s_tpos[t],
+                              (p.tile_first + row_of(j)) * ROW + k * 32 + lane);
     }
     timeline_mark(TL, tl_slot, 3);
 }

@@ -93,11 +93,11 @@ static void launch_small(uint32_t grid, cudaStream_t st, const StepParams &p, bo
 }
 
 /* GRID CTAs (at most one per SM) share out p.fold_tiles rows x p.nslab slabs */
-template <int WARPS, int T, int UNR, int MODE = 0>
+template <int CW, int T, int UNR, bool TL = false>
 static void launch_balanced(uint32_t grid, cudaStream_t st, const StepParams &p, bool pdl) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(WARPS * 32);
+    cfg.blockDim = dim3((CW + 1) * 32); /* CW compute warps and the finisher */
     cfg.dynamicSmemBytes = balanced_smem_bytes(p.src_packs_pad, p.nslab, T, p.fold_tiles, grid);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -109,7 +109,7 @@ static void launch_balanced(uint32_t grid, cudaStream_t st, const StepParams &p,
     }
     cfg.attrs = attr;
     cfg.numAttrs = na;
-    NB_CUDA(cudaLaunchKernelEx(&cfg, balanced_kernel<WARPS, T, UNR, MODE>, p));
+    NB_CUDA(cudaLaunchKernelEx(&cfg, balanced_kernel<CW, T, UNR, TL>, p));
 }
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
@@ -181,11 +181,11 @@ static void launch_variant(uint32_t grid, cudaStream_t st, const StepParams &p, 
         NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)small_world_kernel<WARPS, T, UNR, TL>, \
             launch_small<WARPS, T, UNR, TL>, 0, nullptr, nullptr, nullptr, nullptr, true, false, false       \
     }
-/* the balanced kernel of mid-size Worlds: WARPS warps per CTA, T targets per lane, one CTA per SM */
-#define NB_VARIANT_BALANCED(NAME, WARPS, T, UNR, MODE)                                                       \
+/* the balanced kernel of mid-size Worlds: CW compute warps + 1 finisher warp per CTA, T targets per lane, one CTA per SM */
+#define NB_VARIANT_BALANCED(NAME, CW, T, UNR, TL)                                                            \
     {                                                                                                        \
-        NAME, WARPS * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)balanced_kernel<WARPS, T, UNR, MODE>, \
-            launch_balanced<WARPS, T, UNR, MODE>, 0, nullptr, nullptr, nullptr, nullptr, false, false, true  \
+        NAME, (CW + 1) * 32, T, 64, 0, 1, UNR, 0.0, false, 0, (const void *)balanced_kernel<CW, T, UNR, TL>, \
+            launch_balanced<CW, T, UNR, TL>, 0, nullptr, nullptr, nullptr, nullptr, false, false, true       \
     }
 /* the reference-exact verification kernel for the reference build with LANES SIMD lanes */
 #define NB_VARIANT_EXACT(NAME, LANES)                                                                        \
@@ -220,14 +220,13 @@ static const Variant kVariants[] = {
     NB_VARIANT_SMALL_TL("w16x3t", 16, 3, 2, true),
     NB_VARIANT_SMALL_TL("w32x1t", 32, 1, 2, true),
     /* mid-size Worlds: (row, slab) units shared out evenly over one CTA per SM (balanced_kernel.cuh) */
-    NB_VARIANT_BALANCED("b16x2", 16, 2, 2, 0),
-    NB_VARIANT_BALANCED("b16x1", 16, 1, 2, 0),
-    NB_VARIANT_BALANCED("b32x1", 32, 1, 2, 0),
-    NB_VARIANT_BALANCED("b16x4", 16, 4, 2, 0),
-    NB_VARIANT_BALANCED("b8x4", 8, 4, 2, 0),
-    NB_VARIANT_BALANCED("b32x2", 32, 2, 2, 0),
-    NB_VARIANT_BALANCED("b16x2t", 16, 2, 2, 8),   /* with the per-warp timeline (tools/step_timeline.py) */
-    NB_VARIANT_BALANCED("b16x4t", 16, 4, 2, 8),
+    NB_VARIANT_BALANCED("b15x1", 15, 1, 2, false),
+    NB_VARIANT_BALANCED("b15x2", 15, 2, 2, false),
+    NB_VARIANT_BALANCED("b15x3", 15, 3, 2, false),
+    NB_VARIANT_BALANCED("b15x4", 15, 4, 2, false),
+    NB_VARIANT_BALANCED("b15x1t", 15, 1, 2, true), /* with the per-warp timeline (tools/step_timeline.py) */
+    NB_VARIANT_BALANCED("b15x2t", 15, 2, 2, true),
+    NB_VARIANT_BALANCED("b15x4t", 15, 4, 2, true),
     /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
      * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
     NB_VARIANT_EXACT("ref8", 8),
@@ -458,7 +457,7 @@ static const double kBalancedUnitFixedPacks = 0.5; /* per unit, in packs of work
 static const size_t kBalancedMaxSmem = 220u << 10;
 static void choose_slabs_balanced(Plan &pl, int sm_count, uint32_t forced_slab_len) {
     const uint32_t unr = 4;
-    const uint32_t warps = (uint32_t)pl.var->threads / 32;
+    const uint32_t warps = (uint32_t)pl.var->threads / 32 - 1; /* compute warps: one warp is the finisher */
     pl.group_slabs = 1;
     if (pl.src_packs == 0) {
         pl.slab_packs = unr;
@@ -478,7 +477,7 @@ static void choose_slabs_balanced(Plan &pl, int sm_count, uint32_t forced_slab_l
                 if (ceil_div(pl.src_packs, sp) != n) continue;
                 const uint32_t units = pl.ntiles * n, ctas = std::min<uint32_t>((uint32_t)sm_count, units);
                 if (n > n_lo && balanced_smem_bytes(pl.src_packs_pad, n, pl.var->T, pl.ntiles, ctas) > kBalancedMaxSmem) break;
-                const uint32_t run = ceil_div(ceil_div(units, ctas), warps);
+                const uint32_t run = ceil_div(balanced_geom(pl.ntiles, n, ctas).upc_max, warps);
                 const double cost = run * ((double)sp + kBalancedUnitFixedPacks);
                 if (pass == 0) best = std::min(best, cost);
                 else if (cost <= best * 1.01) best_sp = sp;

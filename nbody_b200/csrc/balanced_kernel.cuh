@@ -17,10 +17,11 @@
  *
  *   - all sources are staged in shared memory once (TMA bulk copies, as in small_kernel.cuh); the targets of the rows
  *     the CTA touches (pos, vel, radius) are staged beside them at kernel entry, off the critical path;
- *   - the CTA's unit list -- its piece of the shared rows FIRST, then its whole rows -- is cut into CW contiguous
- *     runs, one per compute warp.  A warp walks its run with the same pair arithmetic and the same even/odd chains as
- *     the other kernels (interact_pack); consecutive slabs of a row go back to back with the targets in registers, so
- *     a unit boundary costs a slab-sum store and nothing else, and slabs can be short (runs differ by one unit);
+ *   - each of the CW compute warps walks two contiguous runs of units: 1 / CW of the CTA's piece of the shared rows
+ *     FIRST, then 1 / CW of its whole rows (cut so that the totals differ by one unit at most), with the same pair
+ *     arithmetic and the same even/odd chains as the other kernels (interact_pack); consecutive slabs of a row go
+ *     back to back with the targets in registers, so a unit boundary costs a slab-sum store and nothing else, and
+ *     slabs can be short;
  *   - one more warp, the FINISHER, computes no pairs.  It sleeps on an mbarrier until the compute warps have left the
  *     shared part of the list (a few us into the step), then publishes this CTA's slab sums of the shared rows in the
  *     global partial buffer and takes an arrival ticket per row, exactly like step_kernel.cuh; where it is the last
@@ -246,12 +247,21 @@ __global__ void __launch_bounds__((CW + 1) * 32, 1) balanced_kernel(const __grid
     const uint32_t nrow = nsr + geo.whole;         /* staged rows: shared rows, then whole rows    */
     /* launch-local row number of staged row j */
     auto row_of = [&](uint32_t j) { return j < nsr ? geo.whole * G + srow_first + j : c * geo.whole + (j - nsr); };
-    /* compute warps whose run begins inside the shared piece: they tell the finisher when they have left it */
-    uint32_t leavers = 0;
-    for (uint32_t w = 0; w < (uint32_t)CW; w++) {
-        const uint32_t wa = (uint32_t)((uint64_t)w * L / CW), wb = (uint32_t)((uint64_t)(w + 1) * L / CW);
-        leavers += wa < Ls && wb > wa;
-    }
+    /* Every compute warp walks TWO contiguous runs: its 1 / CW of the shared piece first, then its 1 / CW of the
+     * whole rows -- cut so that the two together are 1 / CW of the list to within one unit.  The shared piece is
+     * therefore behind all warps after Ls / L of the pair time, and the finisher has the rest of it for the ticket
+     * chain.  run_cut(w) = units of the whole rows that belong to warps below w. */
+    const uint32_t Lw = L - Ls;
+    auto run_cut = [&](uint32_t w) {
+        uint32_t cut = 0;
+        for (uint32_t v = 1; v <= w; v++) { /* monotone by construction, ends at Lw */
+            const uint32_t want = (uint32_t)((uint64_t)v * L / CW) - (uint32_t)((uint64_t)v * Ls / CW);
+            cut = min(max(cut, want), Lw);
+        }
+        return w == (uint32_t)CW ? Lw : cut;
+    };
+    uint32_t leavers = 0; /* compute warps with at least one shared unit: they tell the finisher when it is done */
+    for (uint32_t w = 0; w < (uint32_t)CW; w++) leavers += (uint32_t)((uint64_t)(w + 1) * Ls / CW) > (uint32_t)((uint64_t)w * Ls / CW);
 
     if (tid == 0) {
         mbar_init(&bar[0], 1);
@@ -295,63 +305,64 @@ __global__ void __launch_bounds__((CW + 1) * 32, 1) balanced_kernel(const __grid
     if (warp < (uint32_t)CW) {
         mbar_wait(&bar[0], 0);
         timeline_mark(TL, tl_slot, 1);
-        /* Compute warp w walks the contiguous run [w L / CW, (w + 1) L / CW) of the unit list. */
-        const uint32_t a = (uint32_t)((uint64_t)warp * L / CW), b = (uint32_t)((uint64_t)(warp + 1) * L / CW);
-        uint32_t j = 0, s = 0; /* staged row and slab of unit a */
-        if (a < Ls) {
-            j = (us0 + a) / p.nslab - srow_first;
-            s = (us0 + a) - (srow_first + j) * p.nslab;
-        } else {
-            j = nsr + (a - Ls) / p.nslab;
-            s = (a - Ls) - (j - nsr) * p.nslab;
-        }
         float2 ntx[T], nty[T], rho[T], ax[T], ay[T];
-        bool fresh = true;
-        for (uint32_t ul = a; ul < b; ul++) {
-            if (fresh) {
-                const uint32_t t = j * ROW + lane;
+#pragma unroll 1
+        for (int phase = 0; phase < 2; phase++) {
+            /* positions [a, b) of the unit list, staged row j and slab s of unit a */
+            uint32_t a, b, j, s;
+            if (phase == 0) {
+                a = (uint32_t)((uint64_t)warp * Ls / CW);
+                b = (uint32_t)((uint64_t)(warp + 1) * Ls / CW);
+                j = (us0 + a) / p.nslab - srow_first;
+                s = (us0 + a) - (srow_first + j) * p.nslab;
+            } else {
+                const uint32_t wa = run_cut(warp), wb = run_cut(warp + 1);
+                a = Ls + wa;
+                b = Ls + wb;
+                j = nsr + wa / p.nslab;
+                s = wa - (j - nsr) * p.nslab;
+            }
+            bool fresh = true;
+            for (uint32_t ul = a; ul < b; ul++) {
+                if (fresh) {
+                    const uint32_t t = j * ROW + lane;
+#pragma unroll
+                    for (int k = 0; k < T; k++) {
+                        const float2 x = s_tpos[t + k * 32];
+                        const float r = s_trad[t + k * 32];
+                        ntx[k] = make_float2(-x.x, -x.x);
+                        nty[k] = make_float2(-x.y, -x.y);
+                        rho[k] = make_float2(r, r);
+                    }
+                }
 #pragma unroll
                 for (int k = 0; k < T; k++) {
-                    const float2 x = s_tpos[t + k * 32];
-                    const float r = s_trad[t + k * 32];
-                    ntx[k] = make_float2(-x.x, -x.x);
-                    nty[k] = make_float2(-x.y, -x.y);
-                    rho[k] = make_float2(r, r);
+                    ax[k] = make_float2(0.f, 0.f);
+                    ay[k] = make_float2(0.f, 0.f);
                 }
-            }
-#pragma unroll
-            for (int k = 0; k < T; k++) {
-                ax[k] = make_float2(0.f, 0.f);
-                ay[k] = make_float2(0.f, 0.f);
-            }
-            const uint32_t pk0 = s * p.slab_packs;
-            const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
+                const uint32_t pk0 = s * p.slab_packs;
+                const uint32_t pk1 = min(pk0 + p.slab_packs, p.src_packs_pad);
 #pragma unroll 1
-            for (uint32_t pk = pk0; pk < pk1; pk += UNR) {
+                for (uint32_t pk = pk0; pk < pk1; pk += UNR) {
 #pragma unroll
-                for (int w = 0; w < UNR; w++) {
-                    const float4 xs = s_xy[2 * (pk + w)];
-                    const float4 ys = s_xy[2 * (pk + w) + 1];
-                    const float4 gs = s_gm[pk + w];
-                    interact_pack<T, kFormPacked>(xs, ys, gs, ntx, nty, rho, ax, ay);
+                    for (int w = 0; w < UNR; w++) {
+                        const float4 xs = s_xy[2 * (pk + w)];
+                        const float4 ys = s_xy[2 * (pk + w) + 1];
+                        const float4 gs = s_gm[pk + w];
+                        interact_pack<T, kFormPacked>(xs, ys, gs, ntx, nty, rho, ax, ay);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < T; k++)
+                    s_part[(size_t)ul * ROW + k * 32 + lane] =
+                        make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
+                fresh = ++s == p.nslab; /* next: the next slab of this row, or the next row */
+                if (fresh) {
+                    s = 0;
+                    j++;
                 }
             }
-#pragma unroll
-            for (int k = 0; k < T; k++)
-                s_part[(size_t)ul * ROW + k * 32 + lane] =
-                    make_float2(__fadd_rn(ax[k].x, ax[k].y), __fadd_rn(ay[k].x, ay[k].y));
-            /* next unit: the next slab of this row, the next row, or -- leaving the shared piece -- the first whole row */
-            fresh = ++s == p.nslab;
-            if (fresh) {
-                s = 0;
-                j++;
-            }
-            if (ul + 1 == Ls) {
-                fresh = true;
-                s = 0;
-                j = nsr;
-            }
-            if (ul + 1 == Ls || (ul + 1 == b && b < Ls)) { /* this warp's last shared unit is done: tell the finisher */
+            if (phase == 0 && b > a) { /* this warp's shared units are done: tell the finisher */
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&bar[1]);
             }

@@ -220,13 +220,13 @@ static const Variant kVariants[] = {
     NB_VARIANT_SMALL_TL("w16x3t", 16, 3, 2, true),
     NB_VARIANT_SMALL_TL("w32x1t", 32, 1, 2, true),
     /* mid-size Worlds: (row, slab) units shared out evenly over one CTA per SM (balanced_kernel.cuh) */
-    NB_VARIANT_BALANCED("b15x1", 15, 1, 2, false),
-    NB_VARIANT_BALANCED("b15x2", 15, 2, 2, false),
-    NB_VARIANT_BALANCED("b15x3", 15, 3, 2, false),
-    NB_VARIANT_BALANCED("b15x4", 15, 4, 2, false),
-    NB_VARIANT_BALANCED("b15x1t", 15, 1, 2, true), /* with the per-warp timeline (tools/step_timeline.py) */
-    NB_VARIANT_BALANCED("b15x2t", 15, 2, 2, true),
-    NB_VARIANT_BALANCED("b15x4t", 15, 4, 2, true),
+    NB_VARIANT_BALANCED("b16x1", 16, 1, 2, false),
+    NB_VARIANT_BALANCED("b16x2", 16, 2, 2, false),
+    NB_VARIANT_BALANCED("b16x3", 16, 3, 2, false),
+    NB_VARIANT_BALANCED("b16x4", 16, 4, 2, false),
+    NB_VARIANT_BALANCED("b16x1t", 16, 1, 2, true), /* with the per-warp timeline (tools/step_timeline.py) */
+    NB_VARIANT_BALANCED("b16x2t", 16, 2, 2, true),
+    NB_VARIANT_BALANCED("b16x4t", 16, 4, 2, true),
     /* verification mode: the reference's AVX / SSE / scalar CPU arithmetic bit for bit (exact_kernel.cuh);
      * NBODY_EXACT=avx|sse|scalar, NB_SIM_FLAG_EXACT (AVX), or NBODY_VARIANT */
     NB_VARIANT_EXACT("ref8", 8),

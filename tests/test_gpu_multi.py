@@ -56,10 +56,10 @@ def test_balanced_kernel_bitwise_equal_across_gpu_counts(nb, oracle, monkeypatch
     if nb.device_count() < gpus:
         pytest.skip(f"needs {gpus} GPUs")
     from nbody_b200.api import FLAG_NO_PEER_STORE
-    monkeypatch.setenv("NBODY_VARIANT", "b15x2")
+    monkeypatch.setenv("NBODY_VARIANT", "b16x2")
     arr, m = oracle.partition(nb.make_galaxies(n, 2))
     one, info1 = _run(nb, arr, m, 4, 0.01, local_gpus=1)
-    assert info1["variant"] == "b15x2"
+    assert info1["variant"] == "b16x2"
     many, _ = _run(nb, arr, m, 4, 0.01, local_gpus=gpus)
     assert many.tobytes() == one.tobytes()
     nccl, _ = _run(nb, arr, m, 4, 0.01, local_gpus=gpus, flags=FLAG_NO_PEER_STORE)

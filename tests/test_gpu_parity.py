@@ -274,7 +274,7 @@ def test_small_world_kernel_equals_step_kernel_bitwise(nb, oracle, monkeypatch, 
 
 
 @pytest.mark.parametrize("n", [1, 33, 250, 1000, 4003, 6000, 12000, 16384, 20000])
-@pytest.mark.parametrize("variant,slab", [("b15x2", 0), ("b15x2", 128), ("b15x1", 0), ("b15x4", 256), ("b15x3", 512), ("b15x4", 0)])
+@pytest.mark.parametrize("variant,slab", [("b16x2", 0), ("b16x2", 128), ("b16x1", 0), ("b16x4", 256), ("b16x3", 512), ("b16x4", 0)])
 def test_balanced_kernel_equals_step_kernel_bitwise(nb, oracle, monkeypatch, n, variant, slab):
     """balanced_kernel.cuh shares (target row, slab) units out evenly over one CTA per SM: rows whose slabs all fall
     into one CTA are added up in shared memory, rows that straddle a CTA boundary through the partial buffer and a

@@ -9,7 +9,7 @@ B=nbody_b200/bin/nbody-bench
 {
 echo "== shipped"
 for n in $SIZES; do timeout 60 $B --gpu --fresh-seed --n $n | tail -1; done
-for v in ${VARIANTS:-b15x1 b15x2 b15x3 b15x4}; do
+for v in ${VARIANTS:-b16x1 b16x2 b16x3 b16x4}; do
   for s in ${SLABS:-0 128 256 512}; do
     echo "== $v slab $s"
     for n in $SIZES; do NBODY_VARIANT=$v NBODY_SLAB=$s timeout 60 $B --gpu --fresh-seed --n $n 2>&1 | tail -1; done

@@ -88,6 +88,9 @@ typedef struct NbSimConfig {
                                      /* order; exact_kernel.cuh) at about a quarter of the fast        */
                                      /* kernels' rate.  env NBODY_EXACT=avx|sse|scalar does the same   */
                                      /* for the reference's three SIMD builds                          */
+#define NB_SIM_FLAG_NO_RESIDENT  32u /* never run chained steps of a tiny World as one launch of one     */
+                                     /* thread-block cluster with the state resident on chip             */
+                                     /* (resident_kernel.cuh; env NBODY_NO_RESIDENT=1 does the same)    */
 #define NB_SIM_FLAG_PERSIST       4u /* run n >= 2 chained steps of a small World as ONE cooperative */
                                      /* launch with a grid barrier between steps (env NBODY_PERSIST=1  */
                                      /* does the same).  Bit-identical to n launches and measured       */
@@ -142,6 +145,9 @@ typedef struct NbSimInfo {
     char variant[16];             /* kernel variant of the plan (NbSimPlanInfo.variant)                         */
     uint64_t graph_launches;      /* cudaGraphLaunch calls so far: chained steps of small Worlds are replayed   */
     uint32_t graph_steps;         /* as CUDA-graph chunks of this many steps (0: this World never uses graphs)  */
+    uint32_t resident_ctas;       /* CTAs of the one cluster that runs n >= 2 chained steps of this (tiny) World */
+                                  /* in one launch, state resident on chip (resident_kernel.cuh); 0: not used   */
+    uint64_t resident_launches;   /* such launches so far (counted in kernels_launched too)                     */
 } NbSimInfo;
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);

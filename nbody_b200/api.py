@@ -20,6 +20,7 @@ FLAG_NO_OVERLAP = 2
 FLAG_PERSIST = 4
 FLAG_NO_GRAPH = 8
 FLAG_EXACT = 16
+FLAG_NO_RESIDENT = 32
 
 
 class WorldData(C.Structure):  # include/nbody_sim.h (ref sim_gpu.h:8-12)
@@ -81,6 +82,8 @@ class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
         ("variant", C.c_char * 16),
         ("graph_launches", C.c_uint64),
         ("graph_steps", C.c_uint32),
+        ("resident_ctas", C.c_uint32),
+        ("resident_launches", C.c_uint64),
     ]
 
     def as_dict(self):

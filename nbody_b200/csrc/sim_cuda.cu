@@ -22,6 +22,7 @@
 #include "nccl_dyn.h"
 #include "persist_kernel.cuh"
 #include "render_kernels.cuh"
+#include "resident_kernel.cuh"
 #include "small_kernel.cuh"
 #include "step_kernel.cuh"
 #include "util.cuh"
@@ -584,6 +585,7 @@ struct Shard { /* one GPU driven by this process */
 namespace nb {
 static const uint32_t kGraphSteps = 20;        /* steps per CUDA-graph chunk (even)                          */
 static const uint32_t kGraphMaxTargets = 4736; /* Worlds up to this size replay chained steps as graph chunks */
+static const uint32_t kResidentMaxTargets = 1536; /* Worlds up to this size run chained steps in one resident cluster */
 }  // namespace nb
 
 /* A chunk of kGraphSteps chained steps of a small World as one instantiated CUDA graph (step_async): valid for one
@@ -615,6 +617,9 @@ struct SimPipeline {
     uint64_t kernels_launched = 0;
     uint64_t persistent_launches = 0; /* of those, cooperative launches of the persistent multi-step kernel */
     uint64_t graph_launches = 0;      /* cudaGraphLaunch calls (each replays kGraphSteps step kernels) */
+    uint32_t resident_ctas = 0;       /* cluster size of the resident multi-step kernel for this World (0: not used) */
+    uint32_t resident_rows = 0;       /* target rows per CTA of that cluster */
+    uint64_t resident_launches = 0;
     cudaDeviceProp prop;
     /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
     std::vector<uint32_t> all_a0, all_a1, all_b0, all_b1;
@@ -762,6 +767,60 @@ static void particle_range_of_tiles(const SimPipeline *sim, uint32_t t0, uint32_
     const uint64_t tile = sim->plan.tile;
     *lo = (uint32_t)std::min<uint64_t>(t0 * tile, limit);
     *hi = (uint32_t)std::min<uint64_t>(t1 * tile, limit);
+}
+
+/* One cluster of up to 16 CTAs runs all n steps of a call (resident_kernel.cuh): tiny Worlds with the T = 1 small-World
+ * plan, on one GPU.  NBODY_RESIDENT_MAX_N moves the size limit (0: never). */
+static void resident_launch_config(SimPipeline *sim, cudaLaunchConfig_t *cfg, cudaLaunchAttribute *attr, bool pdl) {
+    memset(cfg, 0, sizeof *cfg);
+    cfg->gridDim = dim3(sim->resident_ctas);
+    cfg->blockDim = dim3(kResidentWarps * 32);
+    cfg->dynamicSmemBytes = resident_smem_bytes(sim->plan.src_packs_pad, sim->plan.nslab, sim->resident_rows);
+    cfg->stream = sim->shards[0].stream;
+    unsigned na = 0;
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = sim->resident_ctas;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    na++;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg->attrs = attr;
+    cfg->numAttrs = na;
+}
+
+static void setup_resident(SimPipeline *sim, bool allowed) {
+    const Plan &pl = sim->plan;
+    const uint32_t max_n = (uint32_t)env_int("NBODY_RESIDENT_MAX_N", (int)kResidentMaxTargets);
+    sim->resident_ctas = 0;
+    if (!allowed || sim->allow_persist || !pl.var->small || pl.var->T != 1 || sim->total_shards != 1 ||
+        sim->data.total_len > max_n)
+        return;
+    const uint32_t rows = ceil_div(sim->data.total_len, 32u);
+    const uint32_t per = ceil_div(rows, (uint32_t)kResidentMaxCtas);
+    if (per * 32u > (uint32_t)kResidentWarps * 32u) return;
+    sim->resident_rows = per;
+    sim->resident_ctas = ceil_div(rows, per);
+    const size_t smem = resident_smem_bytes(pl.src_packs_pad, pl.nslab, per);
+    const void *func = (const void *)resident_kernel<2>;
+    if (smem > kSmallWorldMaxSmem) {
+        sim->resident_ctas = 0;
+        return;
+    }
+    NB_CUDA(cudaSetDevice(sim->shards[0].device));
+    NB_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallWorldMaxSmem));
+    if (sim->resident_ctas > 8) NB_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[2];
+    resident_launch_config(sim, &cfg, attr, false);
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, func, &cfg) != cudaSuccess || clusters < 1) {
+        (void)cudaGetLastError();
+        sim->resident_ctas = 0; /* this device cannot co-schedule the cluster: launch per step instead */
+    }
 }
 
 static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
@@ -920,6 +979,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
      * small-World plans on one GPU, on a stream we own (a caller's stream may itself be under capture) */
     sim->use_graph = sim->use_graph && sim->total_shards == 1 && pl.var->small && pl.ntiles <= (uint32_t)sim->prop.multiProcessorCount &&
                      sim->shards[0].own_stream && sim->data.total_len <= kGraphMaxTargets;
+    setup_resident(sim, !(cfg.flags & NB_SIM_FLAG_NO_RESIDENT) && !env_int("NBODY_NO_RESIDENT", 0));
     for (Shard &sh : sim->shards) { /* creation-time initialisation done before anything else uses the buffers */
         NB_CUDA(cudaSetDevice(sh.device));
         NB_CUDA(cudaStreamSynchronize(sh.stream));
@@ -1237,6 +1297,25 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         NB_CUDA(cudaEventRecord(sh.ev_begin, sh.stream));
     }
     const bool split = sim->exchange == kExchangeNccl && sim->overlap;
+    if (sim->resident_ctas && n >= 2 && sim->shards[0].a1 == sim->shards[0].b0) {
+        /* a tiny World: all n steps in one launch of one cluster, state resident on chip (resident_kernel.cuh) */
+        Shard &sh = sim->shards[0];
+        NB_CUDA(cudaSetDevice(sh.device));
+        ResidentParams rp;
+        fill_params(sim, 0, dt, &rp.s);
+        rp.s.dst_xy[0] = reinterpret_cast<float *>(sh.src_xy[(sim->cur + (int)(n & 1u)) & 1]); /* where the last step's positions go */
+        rp.src_xy_alt = sh.src_xy[sim->cur ^ 1];
+        rp.nsteps = n;
+        rp.rows_per_cta = sim->resident_rows;
+        cudaLaunchConfig_t cfg;
+        cudaLaunchAttribute attr[2];
+        resident_launch_config(sim, &cfg, attr, sim->pdl);
+        NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2>, rp));
+        sim->kernels_launched++;
+        sim->resident_launches++;
+        sim->cur ^= (int)(n & 1u);
+        n = 0;
+    }
     if (sim->use_graph && n >= 2 && sim->shards[0].a1 == sim->shards[0].b0) {
         static_assert(kGraphSteps % 2 == 0, "a chunk must bring the ping-pong buffers back");
         Shard &sh = sim->shards[0];
@@ -1487,6 +1566,8 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     strncpy(out->variant, sim->plan.var->name, sizeof out->variant - 1);
     out->graph_launches = sim->graph_launches;
     out->graph_steps = sim->use_graph ? nb::kGraphSteps : 0;
+    out->resident_ctas = sim->resident_ctas;
+    out->resident_launches = sim->resident_launches;
     uint32_t tiles = 0;
     for (const nb::Shard &sh : sim->shards) tiles += (sh.a1 - sh.a0) + (sh.b1 - sh.b0);
     out->tiles_local = tiles;

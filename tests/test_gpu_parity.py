@@ -215,7 +215,7 @@ def test_persistent_multi_step_kernel_equals_one_launch_per_step_bitwise(nb, ora
     from nbody_b200.api import FLAG_PERSIST
     monkeypatch.setenv("NBODY_SMALL_MAX_N", "0")   # the persistent kernel is a build of the (tile, slab)-per-CTA kernel
     arr, m = oracle.partition(nb.make_galaxies(n, 2))
-    with nb.SimPipeline(n, m, flags=FLAG_PERSIST) as a, nb.SimPipeline(n, m) as b:
+    with nb.SimPipeline(n, m, flags=FLAG_PERSIST) as a, nb.SimPipeline(n, m) as b:   # NBODY_SMALL_MAX_N=0: no resident path either
         a.set_data(arr)
         b.set_data(arr)
         a.update(steps, 0.01)
@@ -318,9 +318,9 @@ def test_cuda_graph_chunks_equal_stream_launches_bitwise(nb, oracle, n):
     """Chained steps of a small World are replayed as CUDA-graph chunks of 20 steps (step_async); the remainder
     and Worlds above 4 736 targets go launch by launch.  Same kernels, same arguments: same bits -- across odd
     step counts (the chunk must start from either source buffer) and a change of dt (the graph is re-captured)."""
-    from nbody_b200.api import FLAG_NO_GRAPH
+    from nbody_b200.api import FLAG_NO_GRAPH, FLAG_NO_RESIDENT    # (tiny Worlds would take the resident kernel instead)
     arr, m = oracle.partition(nb.make_galaxies(n, 2))
-    with nb.SimPipeline(n, m) as a, nb.SimPipeline(n, m, flags=FLAG_NO_GRAPH) as b:
+    with nb.SimPipeline(n, m, flags=FLAG_NO_RESIDENT) as a, nb.SimPipeline(n, m, flags=FLAG_NO_GRAPH | FLAG_NO_RESIDENT) as b:
         a.set_data(arr)
         b.set_data(arr)
         for steps, dt in ((45, 0.01), (1, 0.01), (61, 0.01), (40, 0.02), (3, 0.02), (20, 0.01)):
@@ -331,6 +331,38 @@ def test_cuda_graph_chunks_equal_stream_launches_bitwise(nb, oracle, n):
     assert ia["graph_steps"] == 20 and ib["graph_steps"] == 0
     assert ia["graph_launches"] == 2 + 3 + 2 + 1 and ib["graph_launches"] == 0
     assert ia["kernels_launched"] == ib["kernels_launched"]        # replayed kernels are counted like launched ones
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 250, 500, 800, 1000, 1200, 1536])
+def test_resident_cluster_kernel_equals_launch_per_step_bitwise(nb, oracle, n):
+    """Chained steps of a tiny World run as ONE launch of ONE thread-block cluster that keeps the whole state on chip
+    (resident_kernel.cuh): positions travel between the CTAs through distributed shared memory, a cluster barrier
+    separates the steps, global memory is read at the start and written at the end.  Same plan and summation order
+    as the small-World kernel: the same bits -- odd and even step counts (either source buffer may be the last),
+    a change of dt, single steps in between (they go launch by launch), massless tails, ragged sizes."""
+    from nbody_b200.api import FLAG_NO_GRAPH, FLAG_NO_RESIDENT
+    arr, m = oracle.partition(nb.make_galaxies(n, 2) if n >= 250 else _cloud(n))
+    with nb.SimPipeline(n, m) as a, nb.SimPipeline(n, m, flags=FLAG_NO_GRAPH | FLAG_NO_RESIDENT) as b:
+        a.set_data(arr)
+        b.set_data(arr)
+        for steps, dt in ((1, 0.01), (7, 0.01), (2, 0.02), (1, 0.02), (100, 0.01), (3, 0.01)):
+            a.update(steps, dt)
+            b.update(steps, dt)
+            assert a.get_data().tobytes() == b.get_data().tobytes(), (steps, dt)
+        ia, ib = a.info(), b.info()
+    rows = -(-n // 32)
+    per_cta = -(-rows // 16)
+    assert ia["resident_ctas"] == -(-rows // per_cta) and ib["resident_ctas"] == 0
+    assert ia["resident_launches"] == 4 and ib["resident_launches"] == 0
+    assert ia["kernels_launched"] < ib["kernels_launched"]
+
+
+def test_worlds_above_the_limit_do_not_take_the_resident_path(nb, oracle):
+    arr, m = oracle.partition(nb.make_galaxies(2000, 2))
+    with nb.SimPipeline(2000, m) as a:
+        a.set_data(arr)
+        a.update(5, 0.01)
+        assert a.info()["resident_ctas"] == 0 and a.info()["resident_launches"] == 0
 
 
 def test_get_between_updates_does_not_disturb_state(nb):

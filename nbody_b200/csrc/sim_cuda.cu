@@ -620,6 +620,7 @@ struct SimPipeline {
     uint32_t resident_ctas = 0;       /* cluster size of the resident multi-step kernel for this World (0: not used) */
     uint32_t resident_rows = 0;       /* target rows per CTA of that cluster */
     uint64_t resident_launches = 0;
+    bool resident_bulk = true;        /* positions between the CTAs as bulk copies (false: remote stores + cluster barrier) */
     cudaDeviceProp prop;
     /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
     std::vector<uint32_t> all_a0, all_a1, all_b0, all_b1;
@@ -805,7 +806,8 @@ static void setup_resident(SimPipeline *sim, bool allowed) {
     sim->resident_rows = per;
     sim->resident_ctas = ceil_div(rows, per);
     const size_t smem = resident_smem_bytes(pl.src_packs_pad, pl.nslab, per);
-    const void *func = (const void *)resident_kernel<2>;
+    sim->resident_bulk = !env_int("NBODY_RESIDENT_ST", 0);
+    const void *func = sim->resident_bulk ? (const void *)resident_kernel<2, true> : (const void *)resident_kernel<2, false>;
     if (smem > kSmallWorldMaxSmem) {
         sim->resident_ctas = 0;
         return;
@@ -1310,7 +1312,8 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         cudaLaunchConfig_t cfg;
         cudaLaunchAttribute attr[2];
         resident_launch_config(sim, &cfg, attr, sim->pdl);
-        NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2>, rp));
+        if (sim->resident_bulk) NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, true>, rp));
+        else NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, false>, rp));
         sim->kernels_launched++;
         sim->resident_launches++;
         sim->cur ^= (int)(n & 1u);

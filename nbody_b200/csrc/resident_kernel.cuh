@@ -1,5 +1,5 @@
 /*
- * resident_kernel.cuh -- n chained steps of a TINY World (N <= ~1 500) in ONE launch of ONE thread-block cluster,
+ * resident_kernel.cuh -- n chained steps of a TINY World (N <= 640) in ONE launch of ONE thread-block cluster,
  * with the whole state of the World resident on chip between steps.
  *
  * UpdateWorld_GPU(w, dt, n) at the reference's own benchmark sizes N = 250 ... 1 200 (ref src/bench.c:38, 100 steps
@@ -23,6 +23,18 @@
  *
  * Same plan, same summation order: bit-identical to n launches of small_world_kernel
  * (tests/test_gpu_parity.py::test_resident_cluster_kernel_equals_launch_per_step_bitwise).
+ *
+ * MEASURED ON B200 (round 2, profiles/r02_resident_kernel.txt; nbody-bench protocol, us per step, 100 steps per call):
+ *       N                 250    500    800   1000   1200   1536   2000
+ *   resident cluster      1.3    1.8    3.0    3.5    4.8    5.9    8.7
+ *   CUDA-graph chunks     2.4    2.5    2.9    3.2    3.2    3.4    4.0
+ *   launch by launch      3.3    3.3    3.4    3.3    3.3    3.4    3.9
+ * A step costs ~1.2 us of fixed latency (pair-loop fill, slab sums, remote stores, cluster barrier) plus the
+ * arithmetic of N x M pairs on at most 16 SMs, which overtakes the 148-SM paths near N = 750: the planner uses it up
+ * to N = 640 (sim_cuda.cu kResidentMaxTargets).  A second build that sent the positions as one bulk copy per peer CTA
+ * (cp.async.bulk shared::cta -> shared::cluster, complete_tx on alternating mbarriers, no cluster barrier) was
+ * bit-identical too and 0.2 ... 1.1 us per step slower at every size (1.5 / 2.2 / 3.7 / 5.6 us at N = 250 / 500 / 800 /
+ * 1 200): at these sizes the exchange is latency, not bandwidth, and a remote store is the shorter path.
  */
 #pragma once
 
@@ -44,7 +56,7 @@ constexpr int kResidentMaxCtas = 16; /* largest (non-portable) cluster on sm_100
 /* dynamic shared memory: xy [2][P][2] float4 | gm [P] float4 | slab sums [rows_per_cta * nslab][32] float2 |
  * target positions [rows_per_cta * 32] float2 | radii [rows_per_cta * 32] float */
 __host__ __device__ inline size_t resident_smem_bytes(uint32_t src_packs_pad, uint32_t nslab, uint32_t rows_per_cta) {
-    return (size_t)src_packs_pad * 80 + (size_t)rows_per_cta * nslab * 32 * sizeof(float2) + (size_t)rows_per_cta * 32 * 12 + 16; /* + 2 mbarriers */
+    return (size_t)src_packs_pad * 80 + (size_t)rows_per_cta * nslab * 32 * sizeof(float2) + (size_t)rows_per_cta * 32 * 12;
 }
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -67,19 +79,7 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t local, uint32_t rank, fl
     asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
 }
 
-/* bulk copy of BYTES from this CTA's shared memory to the same place in CTA RANK, counted on that CTA's mbarrier */
-__device__ __forceinline__ void bulk_s2cluster(uint32_t local, uint32_t bar_local, uint32_t rank, uint32_t bytes) {
-    uint32_t dst, bar;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(dst) : "r"(local), "r"(rank));
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(bar) : "r"(bar_local), "r"(rank));
-    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-                 "r"(local), "r"(bytes), "r"(bar)
-                 : "memory");
-}
-
-/* BULK: the new positions travel as one bulk copy per peer CTA (complete_tx on the peer's mbarrier) instead of
- * scalar remote stores followed by a cluster barrier */
-template <int UNR, bool BULK>
+template <int UNR>
 __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const __grid_constant__ ResidentParams rp) {
     const StepParams &p = rp.s;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -89,23 +89,12 @@ __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const 
     float2 *s_part = reinterpret_cast<float2 *>(s_gm + P);                    /* [rows_per_cta * nslab][32] */
     float2 *s_tpos = s_part + (size_t)rp.rows_per_cta * p.nslab * 32;         /* [rows_per_cta * 32] */
     float *s_trad = reinterpret_cast<float *>(s_tpos + (size_t)rp.rows_per_cta * 32);
-    uint64_t *rx = reinterpret_cast<uint64_t *>(s_trad + (size_t)rp.rows_per_cta * 32); /* BULK: positions received */
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t rank = cluster_ctarank(), C = cluster_nctarank();
     const uint32_t rows = (p.total_len + 31u) / 32u;
     const uint32_t row0 = min(rank * rp.rows_per_cta, rows);
     const uint32_t nrow = min(rows - row0, rp.rows_per_cta);                  /* may be 0: the CTA still keeps the barriers */
-
-    /* BULK: the source packs this CTA owns (its massive targets; rows are 8 whole packs) and what the peers own */
-    const uint32_t mpacks = (p.mass_len + 3u) / 4u;
-    const uint32_t pk_lo = min(row0 * 8u, mpacks), pk_hi = min((row0 + nrow) * 8u, mpacks);
-    const uint32_t rx_bytes = (mpacks - (pk_hi - pk_lo)) * 32u;
-    if (BULK && tid == 0) { /* two barriers, alternating: a peer may be one step ahead, never two */
-        mbar_init(&rx[0], 1);
-        mbar_init(&rx[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
 
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
@@ -134,7 +123,7 @@ __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const 
     const uint32_t units = nrow * p.nslab;
     const uint32_t xy_local = smem_u32(s_xy);
     uint32_t cur = 0;
-    for (uint32_t step = 0;; step++, cur ^= 1u) {
+    for (uint32_t step = 0; step < rp.nsteps; step++, cur ^= 1u) {
         const float4 *xy = s_xy + (size_t)cur * P * 2;
         for (uint32_t u = warp; u < units; u += kResidentWarps) {
             const uint32_t row = u / p.nslab, s = u - row * p.nslab;
@@ -162,7 +151,18 @@ __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const 
             const uint32_t row = tid >> 5;
             const float2 *sums = s_part + (size_t)row * p.nslab * 32 + lane;
             float2 sum = sums[0];
-            for (uint32_t s = 1; s < p.nslab; s++) {
+            uint32_t s = 1;
+            for (; s + 8 <= p.nslab; s += 8) { /* eight loads in flight, added in slab order */
+                float2 v[8];
+#pragma unroll
+                for (int w = 0; w < 8; w++) v[w] = sums[(size_t)(s + w) * 32];
+#pragma unroll
+                for (int w = 0; w < 8; w++) {
+                    sum.x = __fadd_rn(sum.x, v[w].x);
+                    sum.y = __fadd_rn(sum.y, v[w].y);
+                }
+            }
+            for (; s < p.nslab; s++) {
                 const float2 v = sums[(size_t)s * 32];
                 sum.x = __fadd_rn(sum.x, v.x);
                 sum.y = __fadd_rn(sum.y, v.y);
@@ -175,42 +175,16 @@ __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const 
             my_x.y = __fadd_rn(my_x.y, __fmul_rn(my_v.y, p.dt));
             s_tpos[tid] = my_x;
             if (mine && my_i < p.mass_len && step + 1 < rp.nsteps) {
+                /* the next step's source buffer of every CTA of the cluster */
                 const uint32_t o = ((cur ^ 1u) * P * 8u + (my_i >> 2) * 8u + (my_i & 3u)) * 4u;
-                if (BULK) { /* this CTA's own copy of the next source buffer; the peers get theirs below */
-                    float *nx = reinterpret_cast<float *>(smem_raw + o);
-                    nx[0] = my_x.x;
-                    nx[4] = my_x.y;
-                } else { /* the next step's source buffer of every CTA of the cluster */
-                    for (uint32_t c = 0; c < C; c++) {
-                        st_cluster_f32(xy_local + o, c, my_x.x);
-                        st_cluster_f32(xy_local + o + 16u, c, my_x.y);
-                    }
+                for (uint32_t c = 0; c < C; c++) {
+                    st_cluster_f32(xy_local + o, c, my_x.x);
+                    st_cluster_f32(xy_local + o + 16u, c, my_x.y);
                 }
             }
         }
-        if (step + 1 == rp.nsteps) break;
-        if (!BULK) {
-            cluster_sync_all(); /* all new positions have landed everywhere; also this CTA's barrier */
-        } else {
-            /* A peer may overwrite the buffer this CTA has just read only with positions of the NEXT step, and it
-             * cannot start that step before it has this CTA's positions of this one: the data is the barrier. */
-            __syncthreads();
-            uint64_t *bar = &rx[step & 1u];
-            if (tid == 0) {
-                if (rx_bytes) mbar_expect_tx(bar, rx_bytes);
-                else mbar_arrive(bar);
-                if (pk_hi > pk_lo) {
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* our st.shared before the bulk reads */
-                    const uint32_t src = xy_local + ((cur ^ 1u) * P * 2u + pk_lo * 2u) * 16u;
-                    for (uint32_t c = 1; c < C; c++) bulk_s2cluster(src, smem_u32(bar), (rank + c) % C, (pk_hi - pk_lo) * 32u);
-                }
-            }
-            mbar_wait(bar, (step >> 1) & 1u);
-        }
+        if (step + 1 < rp.nsteps) cluster_sync_all(); /* all new positions have landed everywhere; also this CTA's barrier */
     }
-
-    /* no CTA leaves while a bulk copy may still be reading its shared memory */
-    if (BULK) cluster_sync_all();
 
     /* the state after the last step goes back to global memory */
     if (mine) {

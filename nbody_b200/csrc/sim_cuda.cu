@@ -585,7 +585,8 @@ struct Shard { /* one GPU driven by this process */
 namespace nb {
 static const uint32_t kGraphSteps = 20;        /* steps per CUDA-graph chunk (even)                          */
 static const uint32_t kGraphMaxTargets = 4736; /* Worlds up to this size replay chained steps as graph chunks */
-static const uint32_t kResidentMaxTargets = 1536; /* Worlds up to this size run chained steps in one resident cluster */
+static const uint32_t kResidentMaxTargets = 640; /* Worlds up to this size run chained steps in one resident cluster: */
+                                                 /* beyond ~750 the 148-SM paths win (resident_kernel.cuh)           */
 }  // namespace nb
 
 /* A chunk of kGraphSteps chained steps of a small World as one instantiated CUDA graph (step_async): valid for one
@@ -620,7 +621,6 @@ struct SimPipeline {
     uint32_t resident_ctas = 0;       /* cluster size of the resident multi-step kernel for this World (0: not used) */
     uint32_t resident_rows = 0;       /* target rows per CTA of that cluster */
     uint64_t resident_launches = 0;
-    bool resident_bulk = true;        /* positions between the CTAs as bulk copies (false: remote stores + cluster barrier) */
     cudaDeviceProp prop;
     /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
     std::vector<uint32_t> all_a0, all_a1, all_b0, all_b1;
@@ -806,8 +806,7 @@ static void setup_resident(SimPipeline *sim, bool allowed) {
     sim->resident_rows = per;
     sim->resident_ctas = ceil_div(rows, per);
     const size_t smem = resident_smem_bytes(pl.src_packs_pad, pl.nslab, per);
-    sim->resident_bulk = !env_int("NBODY_RESIDENT_ST", 0);
-    const void *func = sim->resident_bulk ? (const void *)resident_kernel<2, true> : (const void *)resident_kernel<2, false>;
+    const void *func = (const void *)resident_kernel<2>;
     if (smem > kSmallWorldMaxSmem) {
         sim->resident_ctas = 0;
         return;
@@ -1312,8 +1311,7 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         cudaLaunchConfig_t cfg;
         cudaLaunchAttribute attr[2];
         resident_launch_config(sim, &cfg, attr, sim->pdl);
-        if (sim->resident_bulk) NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, true>, rp));
-        else NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, false>, rp));
+        NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2>, rp));
         sim->kernels_launched++;
         sim->resident_launches++;
         sim->cur ^= (int)(n & 1u);

@@ -333,14 +333,15 @@ def test_cuda_graph_chunks_equal_stream_launches_bitwise(nb, oracle, n):
     assert ia["kernels_launched"] == ib["kernels_launched"]        # replayed kernels are counted like launched ones
 
 
-@pytest.mark.parametrize("n", [1, 31, 33, 250, 500, 800, 1000, 1200, 1536])
-def test_resident_cluster_kernel_equals_launch_per_step_bitwise(nb, oracle, n):
+@pytest.mark.parametrize("n", [1, 31, 33, 250, 500, 640, 800, 1000, 1200, 1536])
+def test_resident_cluster_kernel_equals_launch_per_step_bitwise(nb, oracle, monkeypatch, n):
     """Chained steps of a tiny World run as ONE launch of ONE thread-block cluster that keeps the whole state on chip
     (resident_kernel.cuh): positions travel between the CTAs through distributed shared memory, a cluster barrier
     separates the steps, global memory is read at the start and written at the end.  Same plan and summation order
     as the small-World kernel: the same bits -- odd and even step counts (either source buffer may be the last),
     a change of dt, single steps in between (they go launch by launch), massless tails, ragged sizes."""
     from nbody_b200.api import FLAG_NO_GRAPH, FLAG_NO_RESIDENT
+    monkeypatch.setenv("NBODY_RESIDENT_MAX_N", "1536")   # planned up to N = 640; the kernel itself is checked beyond
     arr, m = oracle.partition(nb.make_galaxies(n, 2) if n >= 250 else _cloud(n))
     with nb.SimPipeline(n, m) as a, nb.SimPipeline(n, m, flags=FLAG_NO_GRAPH | FLAG_NO_RESIDENT) as b:
         a.set_data(arr)
@@ -358,8 +359,8 @@ def test_resident_cluster_kernel_equals_launch_per_step_bitwise(nb, oracle, n):
 
 
 def test_worlds_above_the_limit_do_not_take_the_resident_path(nb, oracle):
-    arr, m = oracle.partition(nb.make_galaxies(2000, 2))
-    with nb.SimPipeline(2000, m) as a:
+    arr, m = oracle.partition(nb.make_galaxies(800, 2))
+    with nb.SimPipeline(800, m) as a:
         a.set_data(arr)
         a.update(5, 0.01)
         assert a.info()["resident_ctas"] == 0 and a.info()["resident_launches"] == 0

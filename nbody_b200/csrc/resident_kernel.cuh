@@ -50,7 +50,8 @@ struct ResidentParams {
     uint32_t rows_per_cta;    /* target rows (32 targets) per CTA; rows_per_cta * 32 <= threads per CTA                */
 };
 
-constexpr int kResidentWarps = 32;
+constexpr int kResidentWarps = 32; /* at most; a World with few (row, slab) units per CTA runs with 8 or 16 warps: every */
+                                   /* warp of the cluster takes part in the barrier that ends a step                */
 constexpr int kResidentMaxCtas = 16; /* largest (non-portable) cluster on sm_100 */
 
 /* dynamic shared memory: xy [2][P][2] float4 | gm [P] float4 | slab sums [rows_per_cta * nslab][32] float2 |
@@ -79,8 +80,8 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t local, uint32_t rank, fl
     asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
 }
 
-template <int UNR>
-__global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const __grid_constant__ ResidentParams rp) {
+template <int UNR, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_constant__ ResidentParams rp) {
     const StepParams &p = rp.s;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t P = p.src_packs_pad;
@@ -99,11 +100,11 @@ __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const 
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     /* everything this CTA will ever read from global memory */
-    for (uint32_t k = tid; k < P * 2; k += kResidentWarps * 32) {
+    for (uint32_t k = tid; k < P * 2; k += WARPS * 32) {
         s_xy[k] = p.src_xy[k];
         s_xy[(size_t)P * 2 + k] = rp.src_xy_alt[k]; /* padding lanes; the real lanes are rewritten by step 1 before use */
     }
-    for (uint32_t k = tid; k < P; k += kResidentWarps * 32) s_gm[k] = p.src_gm[k];
+    for (uint32_t k = tid; k < P; k += WARPS * 32) s_gm[k] = p.src_gm[k];
     const uint32_t my_i = row0 * 32 + tid;
     const bool mine = tid < nrow * 32 && my_i < p.total_len;
     float2 my_x = make_float2(0.f, 0.f), my_v = make_float2(0.f, 0.f), my_a = make_float2(0.f, 0.f);
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(kResidentWarps * 32, 1) resident_kernel(const 
     uint32_t cur = 0;
     for (uint32_t step = 0; step < rp.nsteps; step++, cur ^= 1u) {
         const float4 *xy = s_xy + (size_t)cur * P * 2;
-        for (uint32_t u = warp; u < units; u += kResidentWarps) {
+        for (uint32_t u = warp; u < units; u += WARPS) {
             const uint32_t row = u / p.nslab, s = u - row * p.nslab;
             const float2 x = s_tpos[row * 32 + lane];
             const float r = s_trad[row * 32 + lane];

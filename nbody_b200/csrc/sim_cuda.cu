@@ -620,6 +620,7 @@ struct SimPipeline {
     uint64_t graph_launches = 0;      /* cudaGraphLaunch calls (each replays kGraphSteps step kernels) */
     uint32_t resident_ctas = 0;       /* cluster size of the resident multi-step kernel for this World (0: not used) */
     uint32_t resident_rows = 0;       /* target rows per CTA of that cluster */
+    uint32_t resident_warps = 32;     /* warps per CTA: 8, 16 or 32, enough for the (row, slab) units of a CTA */
     uint64_t resident_launches = 0;
     cudaDeviceProp prop;
     /* tile ranges of every global shard, for the exchange: massive [A0,A1) */
@@ -775,7 +776,7 @@ static void particle_range_of_tiles(const SimPipeline *sim, uint32_t t0, uint32_
 static void resident_launch_config(SimPipeline *sim, cudaLaunchConfig_t *cfg, cudaLaunchAttribute *attr, bool pdl) {
     memset(cfg, 0, sizeof *cfg);
     cfg->gridDim = dim3(sim->resident_ctas);
-    cfg->blockDim = dim3(kResidentWarps * 32);
+    cfg->blockDim = dim3(sim->resident_warps * 32);
     cfg->dynamicSmemBytes = resident_smem_bytes(sim->plan.src_packs_pad, sim->plan.nslab, sim->resident_rows);
     cfg->stream = sim->shards[0].stream;
     unsigned na = 0;
@@ -793,6 +794,11 @@ static void resident_launch_config(SimPipeline *sim, cudaLaunchConfig_t *cfg, cu
     cfg->numAttrs = na;
 }
 
+static const void *resident_func(uint32_t warps) {
+    return warps == 8 ? (const void *)resident_kernel<2, 8> : warps == 16 ? (const void *)resident_kernel<2, 16>
+                                                                            : (const void *)resident_kernel<2, 32>;
+}
+
 static void setup_resident(SimPipeline *sim, bool allowed) {
     const Plan &pl = sim->plan;
     const uint32_t max_n = (uint32_t)env_int("NBODY_RESIDENT_MAX_N", (int)kResidentMaxTargets);
@@ -806,7 +812,9 @@ static void setup_resident(SimPipeline *sim, bool allowed) {
     sim->resident_rows = per;
     sim->resident_ctas = ceil_div(rows, per);
     const size_t smem = resident_smem_bytes(pl.src_packs_pad, pl.nslab, per);
-    const void *func = (const void *)resident_kernel<2>;
+    const uint32_t units = per * pl.nslab;
+    sim->resident_warps = units <= 8 && per <= 8 ? 8 : units <= 16 && per <= 16 ? 16 : 32;
+    const void *func = resident_func(sim->resident_warps);
     if (smem > kSmallWorldMaxSmem) {
         sim->resident_ctas = 0;
         return;
@@ -1311,7 +1319,9 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         cudaLaunchConfig_t cfg;
         cudaLaunchAttribute attr[2];
         resident_launch_config(sim, &cfg, attr, sim->pdl);
-        NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2>, rp));
+        if (sim->resident_warps == 8) NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, 8>, rp));
+        else if (sim->resident_warps == 16) NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, 16>, rp));
+        else NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, 32>, rp));
         sim->kernels_launched++;
         sim->resident_launches++;
         sim->cur ^= (int)(n & 1u);

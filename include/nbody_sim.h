@@ -169,6 +169,10 @@ typedef struct NbSimPlanInfo {
                              /* slab).  > 1 only where one partial per (slab, target) would exceed the budget */
     uint32_t groups;         /* CTAs per tile = partial sums per target = ceil(slabs / group_slabs); they are */
                              /* added in group order                                                           */
+    uint32_t resident_ctas;  /* one GPU, tiny Worlds: n >= 2 chained steps run as ONE launch of one cluster of */
+                             /* this many CTAs with the state resident on chip (resident_kernel.cuh); 0: no   */
+    uint32_t resident_rows;  /* target rows (32 targets) per CTA of that cluster                               */
+    uint32_t resident_warps; /* warps per CTA of that cluster                                                  */
 } NbSimPlanInfo;
 
 void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm_count, NbSimPlanInfo *out,

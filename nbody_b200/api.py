@@ -53,6 +53,9 @@ class SimPlanInfo(C.Structure):  # include/nbody_sim.h NbSimPlanInfo
         ("ctas_per_sm", C.c_uint32),
         ("group_slabs", C.c_uint32),
         ("groups", C.c_uint32),
+        ("resident_ctas", C.c_uint32),
+        ("resident_rows", C.c_uint32),
+        ("resident_warps", C.c_uint32),
     ]
 
 

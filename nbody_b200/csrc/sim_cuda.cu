@@ -799,26 +799,29 @@ static const void *resident_func(uint32_t warps) {
                                                                             : (const void *)resident_kernel<2, 32>;
 }
 
-static void setup_resident(SimPipeline *sim, bool allowed) {
-    const Plan &pl = sim->plan;
+/* Host-only part of the decision (NbSimPlan reports it too): the cluster that would run chained steps of a World of
+ * N particles under plan PL on one GPU -- CTAs (0: not this World), target rows per CTA, warps per CTA. */
+static void resident_geometry(const Plan &pl, uint32_t N, uint32_t *ctas, uint32_t *rows_per_cta, uint32_t *warps) {
     const uint32_t max_n = (uint32_t)env_int("NBODY_RESIDENT_MAX_N", (int)kResidentMaxTargets);
-    sim->resident_ctas = 0;
-    if (!allowed || sim->allow_persist || !pl.var->small || pl.var->T != 1 || sim->total_shards != 1 ||
-        sim->data.total_len > max_n)
-        return;
-    const uint32_t rows = ceil_div(sim->data.total_len, 32u);
+    *ctas = *rows_per_cta = 0;
+    *warps = kResidentWarps;
+    if (!pl.var->small || pl.var->T != 1 || N == 0 || N > max_n || env_int("NBODY_NO_RESIDENT", 0)) return;
+    const uint32_t rows = ceil_div(N, 32u);
     const uint32_t per = ceil_div(rows, (uint32_t)kResidentMaxCtas);
-    if (per * 32u > (uint32_t)kResidentWarps * 32u) return;
-    sim->resident_rows = per;
-    sim->resident_ctas = ceil_div(rows, per);
-    const size_t smem = resident_smem_bytes(pl.src_packs_pad, pl.nslab, per);
+    if (per > (uint32_t)kResidentWarps) return; /* thread t owns target t of the CTA's rows */
+    if (resident_smem_bytes(pl.src_packs_pad, pl.nslab, per) > kSmallWorldMaxSmem) return;
     const uint32_t units = per * pl.nslab;
-    sim->resident_warps = units <= 8 && per <= 8 ? 8 : units <= 16 && per <= 16 ? 16 : 32;
+    *rows_per_cta = per;
+    *ctas = ceil_div(rows, per);
+    *warps = units <= 8 && per <= 8 ? 8 : units <= 16 && per <= 16 ? 16 : 32;
+}
+
+static void setup_resident(SimPipeline *sim, bool allowed) {
+    sim->resident_ctas = 0;
+    if (!allowed || sim->allow_persist || sim->total_shards != 1) return;
+    resident_geometry(sim->plan, sim->data.total_len, &sim->resident_ctas, &sim->resident_rows, &sim->resident_warps);
+    if (!sim->resident_ctas) return;
     const void *func = resident_func(sim->resident_warps);
-    if (smem > kSmallWorldMaxSmem) {
-        sim->resident_ctas = 0;
-        return;
-    }
     NB_CUDA(cudaSetDevice(sim->shards[0].device));
     NB_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallWorldMaxSmem));
     if (sim->resident_ctas > 8) NB_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
@@ -988,7 +991,7 @@ static SimPipeline *create_pipeline(WorldData data, const NbSimConfig *cfg_in) {
      * small-World plans on one GPU, on a stream we own (a caller's stream may itself be under capture) */
     sim->use_graph = sim->use_graph && sim->total_shards == 1 && pl.var->small && pl.ntiles <= (uint32_t)sim->prop.multiProcessorCount &&
                      sim->shards[0].own_stream && sim->data.total_len <= kGraphMaxTargets;
-    setup_resident(sim, !(cfg.flags & NB_SIM_FLAG_NO_RESIDENT) && !env_int("NBODY_NO_RESIDENT", 0));
+    setup_resident(sim, !(cfg.flags & NB_SIM_FLAG_NO_RESIDENT));
     for (Shard &sh : sim->shards) { /* creation-time initialisation done before anything else uses the buffers */
         NB_CUDA(cudaSetDevice(sh.device));
         NB_CUDA(cudaStreamSynchronize(sh.stream));
@@ -1530,6 +1533,7 @@ void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm
     out->ctas_per_sm = pl.ctas_per_sm;
     out->group_slabs = pl.group_slabs;
     out->groups = pl.var->small ? pl.nslab : pl.ngroups; /* small Worlds: one sum per slab, in shared memory */
+    if (shards == 1) nb::resident_geometry(pl, total_len, &out->resident_ctas, &out->resident_rows, &out->resident_warps);
     if (tile_ranges)
         for (int q = 0; q < shards; q++)
             nb::shard_tiles(pl, shards, q, &tile_ranges[4 * q], &tile_ranges[4 * q + 1], &tile_ranges[4 * q + 2],

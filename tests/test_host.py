@@ -230,3 +230,26 @@ def test_empty_pipeline_is_inert_through_the_reference_seam(nb):
     L.NbSimGetInfo(sim, C.byref(info))
     assert info.total_len == 0 and info.kernels_launched == 0
     L.DestroySimPipeline(sim)
+
+
+def test_tiny_worlds_are_planned_onto_one_resident_cluster(nb, monkeypatch):
+    """Host-only half of the resident-kernel decision (NbSimPlan): Worlds up to 640 particles on one GPU run chained
+    steps as one launch of one cluster of at most 16 CTAs; every target row has a CTA, every target of a CTA a thread,
+    every CTA enough warps for its (row, slab) units or the full 32."""
+    for n in list(range(1, 700, 7)) + [639, 640, 641, 1000, 4000, 20000]:
+        info, _ = nb.plan(n, n // 2, 1, 148)
+        rows = -(-n // 32)
+        if n > 640:
+            assert info["resident_ctas"] == 0, n
+            continue
+        c, per, warps = info["resident_ctas"], info["resident_rows"], info["resident_warps"]
+        assert 1 <= c <= 16 and c * per >= rows > (c - 1) * per, (n, c, per)
+        assert warps in (8, 16, 32) and per <= warps, (n, per, warps)
+        assert warps == 32 or per * info["slabs"] <= warps, (n, per, info["slabs"], warps)
+        assert info["variant"] == "w32x1" and info["tile_targets"] == 32
+    assert nb.plan(500, 250, 2, 148)[0]["resident_ctas"] == 0          # a World split over GPUs: launch per step
+    monkeypatch.setenv("NBODY_NO_RESIDENT", "1")
+    assert nb.plan(500, 250, 1, 148)[0]["resident_ctas"] == 0
+    monkeypatch.delenv("NBODY_NO_RESIDENT")
+    monkeypatch.setenv("NBODY_RESIDENT_MAX_N", "1536")
+    assert nb.plan(1536, 700, 1, 148)[0]["resident_ctas"] == 16

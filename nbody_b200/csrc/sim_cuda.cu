@@ -803,8 +803,7 @@ static const void *resident_func(uint32_t warps) {
  * N particles under plan PL on one GPU -- CTAs (0: not this World), target rows per CTA, warps per CTA. */
 static void resident_geometry(const Plan &pl, uint32_t N, uint32_t *ctas, uint32_t *rows_per_cta, uint32_t *warps) {
     const uint32_t max_n = (uint32_t)env_int("NBODY_RESIDENT_MAX_N", (int)kResidentMaxTargets);
-    *ctas = *rows_per_cta = 0;
-    *warps = kResidentWarps;
+    *ctas = *rows_per_cta = *warps = 0;
     if (!pl.var->small || pl.var->T != 1 || N == 0 || N > max_n || env_int("NBODY_NO_RESIDENT", 0)) return;
     const uint32_t rows = ceil_div(N, 32u);
     const uint32_t per = ceil_div(rows, (uint32_t)kResidentMaxCtas);

@@ -17,6 +17,11 @@ from _oracle import acc_of, mass_len_of, rel_acc_error
 F32 = np.float32
 
 
+
+def _order(info):
+    """What fixes the summation order (everything but HOW chained steps of a tiny World on one GPU are launched)."""
+    return {k: v for k, v in info.items() if not k.startswith("resident_")}
+
 def _fma(a, b, c):
     # exact for FP32 inputs: the product is exact in FP64, one rounding to FP64 and one to FP32
     return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(F32)
@@ -95,7 +100,7 @@ def test_slab_groups_bound_the_partial_buffer(nb, monkeypatch):
             assert info["slab_len"] % 512 == 0 or info["variant"] == "t128x2"     # whole source tiles
         for shards in (2, 8):
             other, _ = nb.plan(n, m, shards)
-            assert other == info
+            assert _order(other) == _order(info)
     one_m, _ = nb.plan(1 << 20, 523884, 1)
     assert one_m["group_slabs"] == 1 and one_m["slabs"] == 37      # the measured N = 1M plan is untouched
     # forced at small N (what the GPU tests use)
@@ -145,6 +150,6 @@ def test_small_worlds_split_their_slabs_over_the_warps_of_one_cta(nb, monkeypatc
         assert info["slabs"] * info["slab_len"] >= m and (info["slabs"] - 1) * info["slab_len"] < m
         assert info["slab_len"] <= 512 and info["slab_len"] % 16 == 0
         assert info["slabs"] <= warps * -(-m // (warps * 512))
-        assert nb.plan(n, m, 2)[0] == info
+        assert _order(nb.plan(n, m, 2)[0]) == _order(info)
     monkeypatch.setenv("NBODY_SMALL_MAX_N", "0")
     assert nb.plan(1000, 485, 1)[0]["variant"] == "t128x2"

@@ -39,6 +39,7 @@
 #pragma once
 
 #include "force_kernel.cuh"
+#include "small_kernel.cuh" /* nb_timeline */
 
 namespace nb {
 
@@ -80,7 +81,10 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t local, uint32_t rank, fl
     asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
 }
 
-template <int UNR, int WARPS>
+/* TL (diagnostics, NBODY_RESIDENT_TL=1, tools/resident_breakdown.py): thread 0 of every CTA adds up the clocks of the
+ * four parts of a step -- its own pair loop, the __syncthreads, slab sums + integrator + remote stores, the cluster
+ * barrier -- and leaves the totals in nb_timeline[rank][0..3]. */
+template <int UNR, int WARPS, bool TL = false>
 __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_constant__ ResidentParams rp) {
     const StepParams &p = rp.s;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -124,8 +128,17 @@ __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_co
     const uint32_t units = nrow * p.nslab;
     const uint32_t xy_local = smem_u32(s_xy);
     uint32_t cur = 0;
+    [[maybe_unused]] long long tl[4] = {0, 0, 0, 0}, tl_t = 0;
+    auto tl_lap = [&](int k) {
+        if (TL && tid == 0) {
+            const long long now = clock64();
+            if (k >= 0) tl[k] += now - tl_t;
+            tl_t = now;
+        }
+    };
     for (uint32_t step = 0; step < rp.nsteps; step++, cur ^= 1u) {
         const float4 *xy = s_xy + (size_t)cur * P * 2;
+        tl_lap(-1);
         for (uint32_t u = warp; u < units; u += WARPS) {
             const uint32_t row = u / p.nslab, s = u - row * p.nslab;
             const float2 x = s_tpos[row * 32 + lane];
@@ -146,7 +159,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_co
             }
             s_part[(size_t)u * 32 + lane] = make_float2(__fadd_rn(ax[0].x, ax[0].y), __fadd_rn(ay[0].x, ay[0].y));
         }
+        tl_lap(0);
         __syncthreads();
+        tl_lap(1);
 
         if (tid < nrow * 32) {
             const uint32_t row = tid >> 5;
@@ -184,8 +199,12 @@ __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_co
                 }
             }
         }
+        tl_lap(2);
         if (step + 1 < rp.nsteps) cluster_sync_all(); /* all new positions have landed everywhere; also this CTA's barrier */
+        tl_lap(3);
     }
+    if (TL && tid == 0)
+        for (int k = 0; k < 4; k++) nb_timeline[rank * 4 + k] = (unsigned long long)tl[k];
 
     /* the state after the last step goes back to global memory */
     if (mine) {

@@ -794,9 +794,15 @@ static void resident_launch_config(SimPipeline *sim, cudaLaunchConfig_t *cfg, cu
     cfg->numAttrs = na;
 }
 
+template <bool TL>
+static const void *resident_func_tl(uint32_t warps) {
+    return warps == 8    ? (const void *)resident_kernel<2, 8, TL>
+           : warps == 16 ? (const void *)resident_kernel<2, 16, TL>
+                         : (const void *)resident_kernel<2, 32, TL>;
+}
+/* NBODY_RESIDENT_TL=1: the builds that record where the clocks of a step go (tools/resident_breakdown.py) */
 static const void *resident_func(uint32_t warps) {
-    return warps == 8 ? (const void *)resident_kernel<2, 8> : warps == 16 ? (const void *)resident_kernel<2, 16>
-                                                                            : (const void *)resident_kernel<2, 32>;
+    return env_int("NBODY_RESIDENT_TL", 0) ? resident_func_tl<true>(warps) : resident_func_tl<false>(warps);
 }
 
 /* Host-only part of the decision (NbSimPlan reports it too): the cluster that would run chained steps of a World of
@@ -1321,9 +1327,8 @@ static void step_async(SimPipeline *sim, uint32_t n, float dt) {
         cudaLaunchConfig_t cfg;
         cudaLaunchAttribute attr[2];
         resident_launch_config(sim, &cfg, attr, sim->pdl);
-        if (sim->resident_warps == 8) NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, 8>, rp));
-        else if (sim->resident_warps == 16) NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, 16>, rp));
-        else NB_CUDA(cudaLaunchKernelEx(&cfg, resident_kernel<2, 32>, rp));
+        void *args[1] = {&rp};
+        NB_CUDA(cudaLaunchKernelExC(&cfg, resident_func(sim->resident_warps), args));
         sim->kernels_launched++;
         sim->resident_launches++;
         sim->cur ^= (int)(n & 1u);

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_co
     cluster_sync_all();
 
     const uint32_t units = nrow * p.nslab;
+    const uint32_t row_w = warp / p.nslab, s_w = warp - row_w * p.nslab;
     const uint32_t xy_local = smem_u32(s_xy);
     uint32_t cur = 0;
     [[maybe_unused]] long long tl[4] = {0, 0, 0, 0}, tl_t = 0;
@@ -139,8 +140,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_co
     for (uint32_t step = 0; step < rp.nsteps; step++, cur ^= 1u) {
         const float4 *xy = s_xy + (size_t)cur * P * 2;
         tl_lap(-1);
+        uint32_t row = row_w, s = s_w; /* of unit `warp`; the next one is WARPS units on (no division in the loop) */
         for (uint32_t u = warp; u < units; u += WARPS) {
-            const uint32_t row = u / p.nslab, s = u - row * p.nslab;
             const float2 x = s_tpos[row * 32 + lane];
             const float r = s_trad[row * 32 + lane];
             float2 ntx[1] = {make_float2(-x.x, -x.x)}, nty[1] = {make_float2(-x.y, -x.y)}, rho[1] = {make_float2(r, r)};
@@ -158,6 +159,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) resident_kernel(const __grid_co
                 }
             }
             s_part[(size_t)u * 32 + lane] = make_float2(__fadd_rn(ax[0].x, ax[0].y), __fadd_rn(ay[0].x, ay[0].y));
+            s += WARPS;
+            while (s >= p.nslab) {
+                s -= p.nslab;
+                row++;
+            }
         }
         tl_lap(0);
         __syncthreads();

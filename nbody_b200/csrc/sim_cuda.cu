@@ -794,11 +794,12 @@ static void resident_launch_config(SimPipeline *sim, cudaLaunchConfig_t *cfg, cu
     cfg->numAttrs = na;
 }
 
+static const int kResidentUnroll = 4; /* packs per pair-loop iteration: the plan's slabs are multiples of 4 packs */
 template <bool TL>
 static const void *resident_func_tl(uint32_t warps) {
-    return warps == 8    ? (const void *)resident_kernel<2, 8, TL>
-           : warps == 16 ? (const void *)resident_kernel<2, 16, TL>
-                         : (const void *)resident_kernel<2, 32, TL>;
+    return warps == 8    ? (const void *)resident_kernel<kResidentUnroll, 8, TL>
+           : warps == 16 ? (const void *)resident_kernel<kResidentUnroll, 16, TL>
+                         : (const void *)resident_kernel<kResidentUnroll, 32, TL>;
 }
 /* NBODY_RESIDENT_TL=1: the builds that record where the clocks of a step go (tools/resident_breakdown.py) */
 static const void *resident_func(uint32_t warps) {

@@ -29,9 +29,13 @@
  *   resident cluster      1.3    1.8    3.0    3.5    4.8    5.9    8.7
  *   CUDA-graph chunks     2.4    2.5    2.9    3.2    3.2    3.4    4.0
  *   launch by launch      3.3    3.3    3.4    3.3    3.3    3.4    3.9
- * A step costs ~1.2 us of fixed latency (pair-loop fill, slab sums, remote stores, cluster barrier) plus the
- * arithmetic of N x M pairs on at most 16 SMs, which overtakes the 148-SM paths near N = 750: the planner uses it up
- * to N = 640 (sim_cuda.cu kResidentMaxTargets).  A second build that sent the positions as one bulk copy per peer CTA
+ * (first version; with four packs per loop iteration and 8 / 16 / 32 warps per CTA: 1.1 / 1.7 us at N = 250 / 500.)
+ * Where a step's clocks go (tools/resident_breakdown.py, profiles/r02_resident_breakdown.txt; thread 0 of a CTA,
+ * 1 000 steps per call): N = 250: 1 835 clk = pair loop 683 + slab sums, integrator, remote stores 493 + cluster
+ * barrier 645; N = 500: 2 918 = 1 139 + 833 + 925; N = 640: 4 657 = 2 749 + 913 + 982.  The pair loop of one 16-source
+ * unit is a latency chain at N = 250 and already the arithmetic of 16 SMs at N = 500 (7.8 K pairs per CTA: 650 clk at
+ * the large kernel's rate), which overtakes the 148-SM paths near N = 750: the planner uses the cluster up to N = 640
+ * (sim_cuda.cu kResidentMaxTargets).  A second build that sent the positions as one bulk copy per peer CTA
  * (cp.async.bulk shared::cta -> shared::cluster, complete_tx on alternating mbarriers, no cluster barrier) was
  * bit-identical too and 0.2 ... 1.1 us per step slower at every size (1.5 / 2.2 / 3.7 / 5.6 us at N = 250 / 500 / 800 /
  * 1 200): at these sizes the exchange is latency, not bandwidth, and a remote store is the shorter path.

@@ -148,6 +148,7 @@ typedef struct NbSimInfo {
     uint32_t resident_ctas;       /* CTAs of the one cluster that runs n >= 2 chained steps of this (tiny) World */
                                   /* in one launch, state resident on chip (resident_kernel.cuh); 0: not used   */
     uint64_t resident_launches;   /* such launches so far (counted in kernels_launched too)                     */
+    uint32_t cluster_split;       /* NbSimPlanInfo.cluster_split of this pipeline                               */
 } NbSimInfo;
 
 void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out);
@@ -173,6 +174,8 @@ typedef struct NbSimPlanInfo {
                              /* this many CTAs with the state resident on chip (resident_kernel.cuh); 0: no   */
     uint32_t resident_rows;  /* target rows (32 targets) per CTA of that cluster                               */
     uint32_t resident_warps; /* warps per CTA of that cluster                                                  */
+    uint32_t cluster_split;  /* small Worlds with few tiles: CTAs (one thread-block cluster) that share the    */
+                             /* slabs of a tile (split_kernel.cuh); 1: one CTA per tile                        */
 } NbSimPlanInfo;
 
 void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm_count, NbSimPlanInfo *out,

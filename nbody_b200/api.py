@@ -56,6 +56,7 @@ class SimPlanInfo(C.Structure):  # include/nbody_sim.h NbSimPlanInfo
         ("resident_ctas", C.c_uint32),
         ("resident_rows", C.c_uint32),
         ("resident_warps", C.c_uint32),
+        ("cluster_split", C.c_uint32),
     ]
 
 
@@ -87,6 +88,7 @@ class SimInfo(C.Structure):  # include/nbody_sim.h NbSimInfo
         ("graph_steps", C.c_uint32),
         ("resident_ctas", C.c_uint32),
         ("resident_launches", C.c_uint64),
+        ("cluster_split", C.c_uint32),
     ]
 
     def as_dict(self):

@@ -24,6 +24,7 @@
 #include "render_kernels.cuh"
 #include "resident_kernel.cuh"
 #include "small_kernel.cuh"
+#include "split_kernel.cuh"
 #include "step_kernel.cuh"
 #include "util.cuh"
 
@@ -111,6 +112,31 @@ static void launch_balanced(uint32_t grid, cudaStream_t st, const StepParams &p,
     cfg.attrs = attr;
     cfg.numAttrs = na;
     NB_CUDA(cudaLaunchKernelEx(&cfg, balanced_kernel<CW, T, UNR, TL>, p));
+}
+
+/* GRID = tiles x CS CTAs in clusters of CS: the CTAs of a cluster share a tile's slabs (split_kernel.cuh) */
+template <int WARPS, int T, int UNR>
+static void launch_small_split(uint32_t grid, uint32_t cs, cudaStream_t st, const StepParams &p, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(WARPS * 32);
+    cfg.dynamicSmemBytes = small_smem_bytes(p.src_packs_pad, p.nslab, T);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    unsigned na = 0;
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cs;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    na++;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    NB_CUDA(cudaLaunchKernelEx(&cfg, small_split_kernel<WARPS, T, UNR>, p));
 }
 
 template <int THREADS, int T, int TJP, int NS, int MINB, int UNR>
@@ -252,6 +278,8 @@ struct Plan {
     uint32_t slab_packs, nslab; /* the slabs: they fix the summation order                              */
     uint32_t group_slabs;       /* consecutive slabs one CTA walks (1: one CTA per slab)                */
     uint32_t ngroups;           /* CTAs per target tile = ceil(nslab / group_slabs) = partials per target */
+    uint32_t csplit;            /* small Worlds with few tiles: CTAs (one cluster) that share a tile's slabs    */
+                                /* (split_kernel.cuh); 1: one CTA per tile.  Not part of the summation order   */
     int ctas_per_sm;
 };
 
@@ -666,8 +694,7 @@ static Tp *dev_alloc(size_t count) {
 
 /* Geometry from sizes alone -- no device is touched, so the same plan can be computed (and
  * tested) on a machine without a GPU.  Occupancy is the variant's __launch_bounds__ promise. */
-static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl,
-                      const Variant *force = nullptr) {
+static void plan_order(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl, const Variant *force) {
     if (const Variant *v = force ? force : forced_variant()) {
         set_geometry(pl, v, N, M);
         choose_slabs(pl, N, sm_count, forced_slab);
@@ -710,6 +737,20 @@ static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab
     pl = best_plan;
 }
 
+/* The plan: the summation order (plan_order) and, where it does not touch that order, how it is launched.  A T = 1
+ * small-World plan whose tiles would leave more than half of the SMs idle shares each tile's slabs over a cluster of
+ * 2 ... 4 CTAs (split_kernel.cuh); NBODY_NO_SPLIT=1 keeps one CTA per tile. */
+static const uint32_t kMaxClusterSplit = 4;
+static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl,
+                      const Variant *force = nullptr) {
+    plan_order(N, M, sm_count, forced_slab, pl, force);
+    pl.csplit = 1;
+    if (!strcmp(pl.var->name, "w32x1") && !env_int("NBODY_NO_SPLIT", 0)) { /* the planned T = 1 small-World kernel */
+        const uint32_t cs = std::min(std::min(kMaxClusterSplit, (uint32_t)sm_count / std::max(1u, pl.ntiles)), pl.nslab);
+        if (cs >= 2) pl.csplit = cs;
+    }
+}
+
 /* Which tiles shard q of S computes: an equal share of the tiles holding massive particles
  * (they feed the exchange) and an equal share of the purely massless tiles. */
 static void shard_tiles(const Plan &pl, int S, int q, uint32_t *a0, uint32_t *a1, uint32_t *b0, uint32_t *b1) {
@@ -717,8 +758,12 @@ static void shard_tiles(const Plan &pl, int S, int q, uint32_t *a0, uint32_t *a1
     split_range(pl.mtiles, pl.ntiles - pl.mtiles, S, q, b0, b1);
 }
 
-/* the kernel a plan runs: the variant itself, or its GROUPED build when a CTA walks several slabs */
-static const void *plan_func(const Plan &pl) { return pl.group_slabs > 1 ? pl.var->func_grouped : pl.var->func; }
+/* the kernel a plan runs: the variant itself, its GROUPED build when a CTA walks several slabs, or the cluster-split
+ * build of the T = 1 small-World kernel */
+static const void *plan_func(const Plan &pl) {
+    if (pl.csplit > 1) return (const void *)small_split_kernel<32, 1, 2>;
+    return pl.group_slabs > 1 ? pl.var->func_grouped : pl.var->func;
+}
 /* what the function is ALLOWED to be launched with: a per-function attribute shared by every pipeline of the process,
  * so for the small-World kernel (shared memory sized per World) it is the cap, not this World's need */
 static size_t plan_smem_limit(const Plan &pl) {
@@ -1244,7 +1289,8 @@ static void launch_tiles(SimPipeline *sim, Shard &sh, StepParams &p, uint32_t t0
      * the last partial lands.  (Released at kernel entry instead, the next step's CTAs were parked early on an
      * uneven set of SMs: N = 4 000 went from 10.3 to 13.7 us per step; released late, 10.3 -> 9.2.) */
     const bool pdl = sim->pdl;
-    if (sim->plan.group_slabs > 1) sim->plan.var->launch_grouped(grid, sh.stream, p, pdl);
+    if (sim->plan.csplit > 1) launch_small_split<32, 1, 2>(grid * sim->plan.csplit, sim->plan.csplit, sh.stream, p, pdl);
+    else if (sim->plan.group_slabs > 1) sim->plan.var->launch_grouped(grid, sh.stream, p, pdl);
     else sim->plan.var->launch(grid, sh.stream, p, pdl);
     NB_CUDA(cudaGetLastError());
     sim->kernels_launched++;
@@ -1538,6 +1584,7 @@ void NbSimPlan(uint32_t total_len, uint32_t mass_len, int32_t shards, int32_t sm
     out->ctas_per_sm = pl.ctas_per_sm;
     out->group_slabs = pl.group_slabs;
     out->groups = pl.var->small ? pl.nslab : pl.ngroups; /* small Worlds: one sum per slab, in shared memory */
+    out->cluster_split = pl.csplit;
     if (shards == 1) nb::resident_geometry(pl, total_len, &out->resident_ctas, &out->resident_rows, &out->resident_warps);
     if (tile_ranges)
         for (int q = 0; q < shards; q++)
@@ -1586,6 +1633,7 @@ void NbSimGetInfo(const SimPipeline *sim, NbSimInfo *out) {
     strncpy(out->variant, sim->plan.var->name, sizeof out->variant - 1);
     out->graph_launches = sim->graph_launches;
     out->graph_steps = sim->use_graph ? nb::kGraphSteps : 0;
+    out->cluster_split = sim->plan.csplit;
     out->resident_ctas = sim->resident_ctas;
     out->resident_launches = sim->resident_launches;
     uint32_t tiles = 0;

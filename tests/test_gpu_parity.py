@@ -358,6 +358,29 @@ def test_resident_cluster_kernel_equals_launch_per_step_bitwise(nb, oracle, monk
     assert ia["kernels_launched"] < ib["kernels_launched"]
 
 
+@pytest.mark.parametrize("n,want", [(33, 1), (250, 4), (700, 4), (1200, 3), (1600, 2), (2000, 2), (2368, 2), (2400, 1), (4003, 1)])
+def test_cluster_split_small_kernel_equals_one_cta_per_tile_bitwise(nb, oracle, monkeypatch, n, want):
+    """Small Worlds whose tiles would leave more than half of the SMs idle share each tile's slabs over a cluster of
+    2 ... 4 CTAs (split_kernel.cuh): the slab sums meet in the first CTA's shared memory through DSMEM and are added
+    in slab order there.  A launch detail, not part of the plan: same bits as one CTA per tile -- single steps,
+    chained steps (CUDA-graph chunks on both sides), a change of dt."""
+    from nbody_b200.api import FLAG_NO_RESIDENT
+    arr, m = oracle.partition(nb.make_galaxies(n, 2) if n >= 250 else _cloud(n))
+    with nb.SimPipeline(n, m, flags=FLAG_NO_RESIDENT) as a:
+        monkeypatch.setenv("NBODY_NO_SPLIT", "1")
+        with nb.SimPipeline(n, m, flags=FLAG_NO_RESIDENT) as b:
+            monkeypatch.delenv("NBODY_NO_SPLIT")
+            ia, ib = a.info(), b.info()
+            assert ia["cluster_split"] == want and ib["cluster_split"] == 1
+            assert (ia["variant"], ia["slab_len"], ia["slabs"]) == (ib["variant"], ib["slab_len"], ib["slabs"])
+            a.set_data(arr)
+            b.set_data(arr)
+            for steps, dt in ((1, 0.01), (45, 0.01), (2, 0.02), (1, 0.02), (23, 0.01)):
+                a.update(steps, dt)
+                b.update(steps, dt)
+                assert a.get_data().tobytes() == b.get_data().tobytes(), (steps, dt)
+
+
 def test_worlds_above_the_limit_do_not_take_the_resident_path(nb, oracle):
     arr, m = oracle.partition(nb.make_galaxies(800, 2))
     with nb.SimPipeline(800, m) as a:

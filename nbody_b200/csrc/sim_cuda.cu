@@ -739,13 +739,16 @@ static void plan_order(uint32_t N, uint32_t M, int sm_count, uint32_t forced_sla
 
 /* The plan: the summation order (plan_order) and, where it does not touch that order, how it is launched.  A T = 1
  * small-World plan whose tiles would leave more than half of the SMs idle shares each tile's slabs over a cluster of
- * 2 ... 4 CTAs (split_kernel.cuh); NBODY_NO_SPLIT=1 keeps one CTA per tile. */
+ * 2 ... 4 CTAs (split_kernel.cuh: the planned T = 1 kernel w32x1 only); NBODY_NO_SPLIT=1 keeps one CTA per tile. */
 static const uint32_t kMaxClusterSplit = 4;
+static const uint32_t kMinSplitPacks = 96; /* below ~380 sources the cluster barrier costs more than the shorter pair
+                                              loop saves (profiles/r02_cluster_split.txt: N = 700 2.8 -> 2.9 us,
+                                              N = 800 2.9 -> 2.7 us) */
 static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl,
                       const Variant *force = nullptr) {
     plan_order(N, M, sm_count, forced_slab, pl, force);
     pl.csplit = 1;
-    if (!strcmp(pl.var->name, "w32x1") && !env_int("NBODY_NO_SPLIT", 0)) { /* the planned T = 1 small-World kernel */
+    if (!strcmp(pl.var->name, "w32x1") && pl.src_packs >= kMinSplitPacks && !env_int("NBODY_NO_SPLIT", 0)) {
         const uint32_t cs = std::min(std::min(kMaxClusterSplit, (uint32_t)sm_count / std::max(1u, pl.ntiles)), pl.nslab);
         if (cs >= 2) pl.csplit = cs;
     }

@@ -46,6 +46,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_split_kernel(const __grid
     const uint32_t pk_first = min(s_first * p.slab_packs, p.src_packs_pad);
     const uint32_t pk_last = min(s_last * p.slab_packs, p.src_packs_pad);
 
+    /* Distributed shared memory may only be touched once every CTA of the cluster is running: arrive now, wait
+     * before the first remote store (after the source copy has landed, so nobody actually waits). */
+    asm volatile("barrier.cluster.arrive.relaxed;" ::: "memory");
     if (tid == 0) {
         mbar_init(bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -93,6 +96,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_split_kernel(const __grid
     }
 
     mbar_wait(bar, 0);
+    asm volatile("barrier.cluster.wait;" ::: "memory"); /* CTA 0 is there: its shared memory may be written */
 
     const uint32_t part_local = smem_u32(s_part);
     for (uint32_t s = s_first + warp; s < s_last; s += WARPS) {

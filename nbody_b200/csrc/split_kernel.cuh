@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_split_kernel(const __grid
     const uint32_t pk_last = min(s_last * p.slab_packs, p.src_packs_pad);
 
     /* Distributed shared memory may only be touched once every CTA of the cluster is running: arrive now, wait
-     * before the first remote store (after the source copy has landed, so nobody actually waits). */
+     * before the first remote store. */
     asm volatile("barrier.cluster.arrive.relaxed;" ::: "memory");
     if (tid == 0) {
         mbar_init(bar, 1);
@@ -95,8 +95,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) small_split_kernel(const __grid
         my_x = p.pos[my_i];
     }
 
-    mbar_wait(bar, 0);
+    /* (the wait costs ~500 clk even when everybody has arrived: it goes here, under the source copy's flight time) */
     asm volatile("barrier.cluster.wait;" ::: "memory"); /* CTA 0 is there: its shared memory may be written */
+    mbar_wait(bar, 0);
 
     const uint32_t part_local = smem_u32(s_part);
     for (uint32_t s = s_first + warp; s < s_last; s += WARPS) {

@@ -741,9 +741,9 @@ static void plan_order(uint32_t N, uint32_t M, int sm_count, uint32_t forced_sla
  * small-World plan whose tiles would leave more than half of the SMs idle shares each tile's slabs over a cluster of
  * 2 ... 4 CTAs (split_kernel.cuh: the planned T = 1 kernel w32x1 only); NBODY_NO_SPLIT=1 keeps one CTA per tile. */
 static const uint32_t kMaxClusterSplit = 4;
-static const uint32_t kMinSplitPacks = 96; /* below ~380 sources the cluster barrier costs more than the shorter pair
-                                              loop saves (profiles/r02_cluster_split.txt: N = 700 2.8 -> 2.9 us,
-                                              N = 800 2.9 -> 2.7 us) */
+static const uint32_t kMinSplitPacks = 112; /* below ~450 sources the two cluster barriers cost what the shorter pair
+                                               loop saves (profiles/r02_cluster_split.txt: N = 700 2.8 -> 3.0 us,
+                                               N = 800 2.8 -> 2.8, N = 1 000 3.1 -> 3.0, N = 2 000 3.9 -> 3.5) */
 static void plan_host(uint32_t N, uint32_t M, int sm_count, uint32_t forced_slab, Plan &pl,
                       const Variant *force = nullptr) {
     plan_order(N, M, sm_count, forced_slab, pl, force);

@@ -358,7 +358,7 @@ def test_resident_cluster_kernel_equals_launch_per_step_bitwise(nb, oracle, monk
     assert ia["kernels_launched"] < ib["kernels_launched"]
 
 
-@pytest.mark.parametrize("n,want", [(250, 1), (700, 1), (800, 4), (1000, 4), (1200, 3), (1600, 2), (2000, 2), (2368, 2), (2400, 1), (4003, 1)])
+@pytest.mark.parametrize("n,want", [(250, 1), (800, 1), (1000, 4), (1200, 3), (1600, 2), (2000, 2), (2368, 2), (2400, 1), (4003, 1)])
 def test_cluster_split_small_kernel_equals_one_cta_per_tile_bitwise(nb, oracle, monkeypatch, n, want):
     """Small Worlds whose tiles would leave more than half of the SMs idle share each tile's slabs over a cluster of
     2 ... 4 CTAs (split_kernel.cuh): the slab sums meet in the first CTA's shared memory through DSMEM and are added

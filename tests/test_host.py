@@ -259,7 +259,7 @@ def test_small_worlds_with_few_tiles_split_their_tiles_over_a_cluster(nb, monkey
     """Host-only: the T = 1 small-World plan shares a tile's slabs over a cluster of min(4, SMs / tiles) CTAs when that
     is at least 2 and the World has enough sources for the shorter pair loop to pay for the cluster barrier.  It is a
     launch detail: variant, slab length and slab count -- the summation order -- are the same with and without."""
-    for n, m, want in [(250, 120, 1), (700, 337, 1), (800, 386, 4), (1000, 485, 4), (1200, 586, 3), (1600, 779, 2),
+    for n, m, want in [(250, 120, 1), (700, 337, 1), (800, 386, 1), (1000, 485, 4), (1200, 586, 3), (1600, 779, 2),
                        (2368, 1151, 2), (2400, 1182, 1), (4736, 2300, 1), (6000, 2951, 1), (20000, 9956, 1)]:
         info, _ = nb.plan(n, m, 1, 148)
         assert info["cluster_split"] == want, (n, info)

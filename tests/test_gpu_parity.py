@@ -381,6 +381,34 @@ def test_cluster_split_small_kernel_equals_one_cta_per_tile_bitwise(nb, oracle, 
                 assert a.get_data().tobytes() == b.get_data().tobytes(), (steps, dt)
 
 
+@pytest.mark.parametrize("massive", ["none", "all"])
+def test_resident_and_split_paths_without_massless_or_without_massive_particles(nb, oracle, massive):
+    """mass_len = 0 (only padding sources: every acceleration is exactly zero, particles drift) and mass_len =
+    total_len, through the resident cluster (N = 300, chained) and the cluster split (N = 1 900, single and chained)."""
+    from nbody_b200.api import FLAG_NO_GRAPH, FLAG_NO_RESIDENT
+    for n in (300, 1900):
+        ps = _cloud(n)
+        ps["mass"] = 0.0 if massive == "none" else np.maximum(ps["mass"], 5.0)
+        arr, m = oracle.partition(ps)
+        assert m == (0 if massive == "none" else n)
+        with nb.SimPipeline(n, m) as a:
+            import os
+            os.environ["NBODY_NO_SPLIT"] = "1"
+            try:
+                b = nb.SimPipeline(n, m, flags=FLAG_NO_GRAPH | FLAG_NO_RESIDENT)
+            finally:
+                del os.environ["NBODY_NO_SPLIT"]
+            with b:
+                a.set_data(arr)
+                b.set_data(arr)
+                for steps in (1, 6, 3):
+                    a.update(steps, 0.01)
+                    b.update(steps, 0.01)
+                    assert a.get_data().tobytes() == b.get_data().tobytes(), (n, steps)
+                if massive == "none":
+                    assert not a.get_data()["ax"].any()
+
+
 def test_worlds_above_the_limit_do_not_take_the_resident_path(nb, oracle):
     arr, m = oracle.partition(nb.make_galaxies(800, 2))
     with nb.SimPipeline(800, m) as a:

@@ -31,11 +31,15 @@ $(OBJ)/sim_cuda.o: $(SRC)/sim_cuda.cu $(CUH)
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/sim_cuda.ptxas.log || (cat $(OBJ)/sim_cuda.ptxas.log; false)
 
+$(OBJ)/noalloc.o: $(SRC)/noalloc.cu $(SRC)/force_kernel.cuh $(wildcard include/*.h)
+	@mkdir -p $(OBJ)
+	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $(OBJ)/noalloc.ptxas.log || (cat $(OBJ)/noalloc.ptxas.log; false)
+
 $(OBJ)/%.o: $(SRC)/%.c $(wildcard include/*.h)
 	@mkdir -p $(OBJ)
 	$(CC) $(CFLAGS) -c $< -o $@
 
-$(LIB): $(OBJ)/sim_cuda.o $(OBJ)/world.o $(OBJ)/galaxy.o
+$(LIB): $(OBJ)/sim_cuda.o $(OBJ)/noalloc.o $(OBJ)/world.o $(OBJ)/galaxy.o
 	@mkdir -p $(dir $@)
 	$(NVCC) $(ARCH) -ccbin $(CXX) -shared -cudart static -o $@ $^ -Xlinker -Bsymbolic -lgomp -ldl -lm
 

@@ -209,6 +209,29 @@ void NbSimAccF64(SimPipeline *sim, uint32_t first, uint32_t last, double *out);
  * last unit done, end.  Copies [warps][4] values of the last such launch on the current device; returns the warps. */
 uint32_t NbSimDebugTimeline(uint64_t *out, uint32_t max_warps);
 
+/*
+ * One step of the hot path WITHOUT any device-memory allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  No pipeline object: D_IN and D_OUT are the caller's own device-accessible arrays of
+ * TOTAL_LEN 32-byte Particles in World order (the MASS_LEN massive particles first); D_OUT receives the state after
+ * one step of length DT (pos, vel, acc; mass and radius copied) and must not be D_IN (a step reads OLD positions).
+ * The work is enqueued on STREAM (a cudaStream_t; NULL: the default stream) of the CURRENT device and not waited for.
+ *
+ * The scratch the kernel needs (slab partials and arrival tickets, nbody_b200/csrc/noalloc.cu) is a static __device__
+ * array of 4 MiB + 256 B that every GPU which loads the library holds until exit; it limits the call to
+ * NB_NOALLOC_MAX_PARTICLES particles.  The function calls no cudaMalloc, cudaFree or allocating library routine.
+ * All calls share the array: calls that overlap on the GPU (two streams, two host threads) race on it.  The first call
+ * on each device looks the array's device address up (cudaGetSymbolAddress) and should be made outside graph capture.
+ *
+ * Returns 0 on success; 1 for arguments it rejects (more than NB_NOALLOC_MAX_PARTICLES particles, mass_len >
+ * total_len, null or identical arrays); 2 for a CUDA error.  A message goes to stderr; the process is not aborted.
+ * Same arithmetic as the other kernels (force_kernel.cuh) with slabs of 512 sources: agrees with UpdateWorld_GPU to
+ * FP32 rounding (tests/test_zz_no_alloc.py), not bit for bit.
+ */
+#define NB_NOALLOC_MAX_PARTICLES 16384u
+int32_t NbStepNoAlloc(const Particle *d_in, Particle *d_out, uint32_t total_len, uint32_t mass_len, float dt,
+                      void *stream);
+
 #ifdef __cplusplus
 }
 #endif

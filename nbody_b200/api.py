@@ -145,6 +145,7 @@ def lib():
         "NbSimDiagnostics": (None, [vp, vp]),
         "NbSimAccF64": (None, [vp, u32, u32, vp]),
         "NbSimDebugTimeline": (u32, [vp, u32]),
+        "NbStepNoAlloc": (C.c_int32, [vp, vp, u32, u32, f32, vp]),
         "NbSimFitCamera": (None, [vp, C.c_int32, C.c_int32, C.POINTER(f32), C.POINTER(f32), C.POINTER(f32)]),
         "NbSimRenderRGBA": (None, [vp, C.c_int32, C.c_int32, f32, f32, f32, f32, vp]),
         # world.c extras

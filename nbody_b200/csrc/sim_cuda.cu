@@ -571,6 +571,23 @@ static const Variant *small_variant_for(uint32_t N, int sm_count) {
     return find_variant(name);
 }
 
+/*
+ * Which Worlds take the balanced kernel (balanced_kernel.cuh): the mid sizes the small-World kernel leaves out -- T = 3, 4
+ * with too few tiles for the SMs, and T = 5, 6 -- where the (tile, slab)-per-CTA kernel runs a fraction of a wave too
+ * many.  Measured on B200 (profiles/r02_balanced_v4_bands.txt, us per step, (tile, slab) kernel -> b16x2): N = 9 500
+ * 21.5 -> 19.5; 10 500 25.0 -> 22.5; 11 000 27.4 -> 23.8; 14 700 42.2 -> 39.5; 19 000 65.4 -> 62.3; 20 000 72.0 -> 68.1;
+ * 22 000 84.1 -> 81.8; 24 000 98.0 -> 95.3; a tie at 10 000, 14 300, 21 000 and 23 000; a loss from 25 000 up.
+ * NBODY_SMALL_MAX_N caps it like the small-World kernel; NBODY_NO_BALANCED=1 switches it off.
+ */
+static const uint32_t kBalancedMaxTargets = 24000;
+static const Variant *balanced_variant_for(uint32_t N, int sm_count) {
+    const char *e = getenv("NBODY_SMALL_MAX_N");
+    if (e && *e && N > (uint32_t)strtoul(e, nullptr, 10)) return nullptr;
+    if (getenv("NBODY_NO_BALANCED") && atoi(getenv("NBODY_NO_BALANCED"))) return nullptr;
+    if (N <= 64u * (uint32_t)sm_count || N > kBalancedMaxTargets) return nullptr; /* T <= 2: the small-World kernel */
+    return find_variant("b16x2");
+}
+
 static const Variant *forced_variant() {
     if (const char *x = getenv("NBODY_EXACT")) { /* reference-exact verification mode, by SIMD build of the reference */
         if (!strcmp(x, "avx") || !strcmp(x, "8") || !strcmp(x, "1") || !strcmp(x, "on")) return find_variant("ref8");
@@ -711,6 +728,14 @@ static void plan_order(uint32_t N, uint32_t M, int sm_count, uint32_t forced_sla
         set_geometry(cand, v, N, M);
         choose_slabs(cand, N, sm_count, forced_slab);
         if (small_smem_bytes(cand.src_packs_pad, cand.nslab, v->T) <= kSmallWorldMaxSmem) {
+            pl = cand;
+            return;
+        }
+    } else if (const Variant *b = balanced_variant_for(N, sm_count)) {
+        Plan cand{};
+        set_geometry(cand, b, N, M);
+        choose_slabs(cand, N, sm_count, forced_slab);
+        if (balanced_plan_smem(cand, sm_count) <= kBalancedMaxSmem) {
             pl = cand;
             return;
         }

@@ -263,7 +263,7 @@ def test_small_worlds_with_few_tiles_split_their_tiles_over_a_cluster(nb, monkey
                        (2368, 1151, 2), (2400, 1182, 1), (4736, 2300, 1), (6000, 2951, 1), (20000, 9956, 1)]:
         info, _ = nb.plan(n, m, 1, 148)
         assert info["cluster_split"] == want, (n, info)
-        assert info["cluster_split"] * info["tiles"] <= 148
+        assert info["cluster_split"] == 1 or info["cluster_split"] * info["tiles"] <= 148
         monkeypatch.setenv("NBODY_NO_SPLIT", "1")
         plain, _ = nb.plan(n, m, 1, 148)
         monkeypatch.delenv("NBODY_NO_SPLIT")

@@ -104,6 +104,7 @@ def test_slab_groups_bound_the_partial_buffer(nb, monkeypatch):
     one_m, _ = nb.plan(1 << 20, 523884, 1)
     assert one_m["group_slabs"] == 1 and one_m["slabs"] == 37      # the measured N = 1M plan is untouched
     # forced at small N (what the GPU tests use)
+    monkeypatch.setenv("NBODY_SMALL_MAX_N", "0")   # N = 20 000 would otherwise take the balanced kernel
     base, _ = nb.plan(20000, 9956, 1)
     per_partial = base["tiles"] * base["tile_targets"] * 8
     for want in (1, 3, 5):
@@ -136,8 +137,8 @@ def test_small_worlds_split_their_slabs_over_the_warps_of_one_cta(nb, monkeypatc
     of equal length, at most 512 sources, one (or k) per warp; the order of summation is still 'slabs in slab order'
     (group_slabs == 1) and does not depend on the shard count."""
     want = {1: "w32x1", 250: "w32x1", 1000: "w32x1", 4003: "w32x1", 4736: "w32x1", 4737: "w16x2", 6000: "w16x2",
-            9472: "w16x2", 9473: "t128x2", 10000: "t128x2", 12000: "w16x3", 14208: "w16x3", 14209: "t128x2",
-            16384: "w16x4", 18944: "w16x4", 18945: "t128x2"}
+            9472: "w16x2", 9473: "b16x2", 10000: "b16x2", 12000: "w16x3", 14208: "w16x3", 14209: "b16x2",
+            16384: "w16x4", 18944: "w16x4", 18945: "b16x2", 24000: "b16x2", 24001: "t128x2"}
     for n, variant in want.items():
         m = max(1, n // 2)
         info, _ = nb.plan(n, m, 1)

@@ -16,7 +16,7 @@ def _run(nb, arr, m, steps, dt, **kw):
     return out, info
 
 
-@pytest.mark.parametrize("n", [6000, 50000, 300000])
+@pytest.mark.parametrize("n", [6000, 20000, 50000, 300000])   # 20 000: the balanced plan
 @pytest.mark.parametrize("gpus", [2, 4, 8])
 def test_single_process_multi_gpu_bitwise_equal_to_one_gpu(nb, oracle, n, gpus):
     if nb.device_count() < gpus:

@@ -1,6 +1,9 @@
 /*
  * balanced_kernel.cuh -- the step kernel of MID-SIZE Worlds (N ~ 5 K ... 30 K): one CTA per SM, every CTA the same
- * number of (target row, slab) units, whatever N is.
+ * number of (target row, slab) units, whatever N is.  Planned (variant b16x2, sim_cuda.cu balanced_variant_for) for the
+ * sizes below N = 24 000 that the small-World kernel leaves out -- 9 473 ... 11 100, 14 209 ... 14 800, 18 945 ... 24 000
+ * at M ~ N / 2 -- where it is 3 ... 13 % faster than the (tile, slab) kernel (profiles/r02_balanced_v4_bands.txt);
+ * elsewhere the other two kernels win.
  *
  * Between the small Worlds (small_kernel.cuh: one CTA per tile of 32 T targets, at most one CTA per SM) and the
  * throughput regime (step_kernel.cuh: thousands of (tile, slab) CTAs in full waves) the step is quantised by the
